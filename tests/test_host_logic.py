@@ -1,0 +1,263 @@
+"""Host logic (no GPU): template preparation, the kernels' per-nonce arithmetic replayed on the
+CPU through tests/host_harness.cpp, the Python template module, the C-ABI symbol table, and the
+miner.py mirror's control flow with a stubbed context."""
+import ctypes as C
+import hashlib
+import os
+import random
+import re
+import sys
+
+import pytest
+
+from oracle import upow_oracle as O
+from conftest import ROOT, has_gpu
+
+
+class Tail(C.Structure):
+    _fields_ = [("mid", C.c_uint32 * 8), ("w", C.c_uint32 * 16), ("pre", C.c_uint32 * 8), ("layout", C.c_uint32),
+                ("pad", C.c_uint32)]
+
+
+class Rule(C.Structure):
+    _fields_ = [("want", C.c_uint32 * 8), ("n_target", C.c_uint32), ("frac_index", C.c_uint32),
+                ("charset_count", C.c_uint32), ("sub0", C.c_uint32), ("range0", C.c_uint32)]
+
+
+def _prepare(hh, prefix, prev_hash_hex, n_int, cc):
+    t, r = Tail(), Rule()
+    rc = hh.hh_prepare(prefix, len(prefix), bytes.fromhex(prev_hash_hex), n_int, cc, C.byref(t), C.byref(r))
+    return rc, t, r
+
+
+def test_struct_sizes(host_harness):
+    a, b = C.c_int(), C.c_int()
+    host_harness.hh_sizes(C.byref(a), C.byref(b))
+    assert a.value == C.sizeof(Tail) and b.value == C.sizeof(Rule)
+
+
+def test_host_sha256(host_harness):
+    rng = random.Random(3)
+    for n in (0, 3, 55, 56, 64, 108, 138, 777):
+        m = rng.randbytes(n)
+        out = C.create_string_buffer(32)
+        host_harness.hh_sha256(m, n, out)
+        assert out.raw == hashlib.sha256(m).digest()
+
+
+@pytest.mark.parametrize("version", [1, 2])
+def test_midstate_tail_and_hot_path(host_harness, version):
+    """Tail::mid/w/pre and the PRMT word builders give hashlib's digest word 0 for every nonce shape."""
+    host_harness.hh_hot_a64.restype = C.c_uint32
+    host_harness.hh_strided_a64.restype = C.c_uint32
+    rng = random.Random(10 + version)
+    for trial in range(20):
+        prefix = rng.randbytes(134 if version == 1 else 104)
+        rc, t, r = _prepare(host_harness, prefix, O.T0_PREV_HASH, 5, 16)
+        assert rc == 0 and t.layout == version
+        py_mid, py_tail = O.midstate_and_tail(prefix)
+        assert list(t.mid) == py_mid
+        assert b"".join(x.to_bytes(4, "big") for x in t.w) == py_tail
+        nonces = [0, 1, 0xff, 0x100, 0xffff, 0x10000, 0x00ff00ff, 0xff00ff00, 0x12345678, 0xffffffff] + \
+                 [rng.getrandbits(32) for _ in range(20)]
+        for nonce in nonces:
+            want = hashlib.sha256(prefix + nonce.to_bytes(4, "little")).digest()
+            d = (C.c_uint32 * 8)()
+            host_harness.hh_full_digest(C.byref(t), nonce, d)
+            assert b"".join(x.to_bytes(4, "big") for x in d) == want
+            w0 = int.from_bytes(want[:4], "big")
+            assert (host_harness.hh_hot_a64(C.byref(t), nonce) + t.mid[0]) & 0xffffffff == w0
+            assert (host_harness.hh_strided_a64(C.byref(t), nonce) + t.mid[0]) & 0xffffffff == w0
+
+
+def test_rule_nibble_form_matches_reference_rule(host_harness):
+    """rule_accepts == miner.py's string predicate for every N in 0..17 x every fraction, on digests
+    engineered to be near the decision boundary; and the word-0 pre-filter never rejects a valid digest
+    and is exact for N < 8."""
+    rng = random.Random(5)
+    prev = O.T0_PREV_HASH
+    prefix = O.t0_prefix(4.0)
+    for n in range(0, 18):
+        for k in range(10):
+            d = float(f"{n}.{k}")
+            rule = O.Rule(d, prev)
+            rc, t, r = _prepare(host_harness, prefix, prev, rule.int_difficulty, rule.charset_count)
+            assert rc == 0
+            assert r.n_target == len(rule.target_prefix)
+            for trial in range(60):
+                # start from the target, then damage 0-2 nibbles near the boundary
+                hexd = list(rule.target_prefix + "".join(rng.choice("0123456789abcdef") for _ in range(64)))[:64]
+                for _ in range(rng.randrange(0, 3)):
+                    pos = min(63, max(0, len(rule.target_prefix) + rng.randrange(-3, 2)))
+                    hexd[pos] = rng.choice("0123456789abcdef")
+                hexd = "".join(hexd)
+                words = (C.c_uint32 * 8)(*[int(hexd[8 * i:8 * i + 8], 16) for i in range(8)])
+                want = rule.is_valid_hex(hexd)
+                assert bool(host_harness.hh_rule_accepts(C.byref(r), words)) == want, (d, hexd)
+                a64 = (words[0] - t.mid[0]) & 0xffffffff
+                pre = bool(host_harness.hh_prefilter(C.byref(r), a64))
+                if want:
+                    assert pre
+                if 1 <= n < 8:
+                    assert pre == want, (d, hexd)
+
+
+def test_prepare_rejects_bad_arguments(host_harness):
+    p = O.t0_prefix(4.0)
+    assert _prepare(host_harness, p[:-1], O.T0_PREV_HASH, 4, 16)[0] != 0   # 133 bytes
+    assert _prepare(host_harness, p, O.T0_PREV_HASH, 4, 0)[0] != 0
+    assert _prepare(host_harness, p, O.T0_PREV_HASH, 4, 17)[0] != 0
+    assert _prepare(host_harness, p, O.T0_PREV_HASH, -1, 16)[0] != 0
+    assert _prepare(host_harness, p, O.T0_PREV_HASH, 64, 8)[0] != 0    # digest_hex[64] would raise in the reference
+    assert _prepare(host_harness, p, O.T0_PREV_HASH, 70, 16)[0] == 0   # s[-70:] is the whole string
+
+
+def test_timestamp_helpers(host_harness):
+    host_harness.hh_get_timestamp.restype = C.c_uint32
+    for version in (1, 2):
+        p = bytearray(O.t0_prefix(4.0, version))
+        buf = (C.c_uint8 * len(p)).from_buffer(p)
+        assert host_harness.hh_get_timestamp(buf, len(p)) == O.T0_TIMESTAMP
+        host_harness.hh_set_timestamp(buf, len(p), O.T0_TIMESTAMP + 5)
+        assert bytes(p) == O.set_timestamp(O.t0_prefix(4.0, version), O.T0_TIMESTAMP + 5)
+
+
+def test_python_template_module_matches_oracle(mine_block_vectors):
+    from upow_b200 import template as T
+    for v in mine_block_vectors:
+        p = v["mining_params"]
+        prev = p["last_block"].get("hash", T.GENESIS_PREV_HASH)
+        rule = T.DifficultyRule.derive(p["difficulty"], prev)
+        ref = O.Rule(p["difficulty"], prev)
+        assert (rule.n_int, rule.charset_count, rule.target_prefix) == \
+               (ref.int_difficulty, ref.charset_count, ref.target_prefix)
+        prefix = T.build_block_prefix(prev, T.string_to_bytes(v["wallet"]),
+                                      T.calculate_merkle_root(p["pending_transactions_hashes"]), v["timestamp"],
+                                      p["difficulty"])
+        assert prefix.hex() == v["block_content"][:-8]
+        assert rule.accepts(v["digest"])
+        assert T.with_timestamp(prefix, v["timestamp"] + 3) == O.set_timestamp(prefix, v["timestamp"] + 3)
+
+
+def test_library_exports_every_declared_symbol():
+    import upow_b200
+    header = open(os.path.join(ROOT, "include", "upow_b200.h")).read()
+    declared = set(re.findall(r"\b(upow_[a-z0-9_]+)\s*\(", header))
+    assert {"upow_init", "upow_set_template", "upow_search_min", "upow_sweep", "upow_search_batch", "upow_cancel",
+            "upow_selftest", "upow_destroy", "upow_last_error"} <= declared
+    lib = upow_b200.load()
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/upow_b200.h but not exported"
+    assert b"sm_100a" in lib.upow_version()
+
+
+def test_ctypes_struct_layouts_match_header():
+    """Field-by-field size check of the ctypes mirrors against a C compile of the header."""
+    import subprocess, tempfile
+    from upow_b200 import _lib
+    src = '#include <stdio.h>\n#include "upow_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu\\n",' \
+          'sizeof(upow_limits),sizeof(upow_result),sizeof(upow_device_info),sizeof(upow_microbench_result),' \
+          'sizeof(upow_template),sizeof(upow_batch_item),__builtin_offsetof(upow_result,hashes_done));return 0;}'
+    with tempfile.TemporaryDirectory() as td:
+        c = os.path.join(td, "s.c")
+        open(c, "w").write(src)
+        exe = os.path.join(td, "s")
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), "-o", exe, c])
+        sizes = list(map(int, subprocess.check_output([exe]).split()))
+    assert sizes == [C.sizeof(_lib.Limits), C.sizeof(_lib.Result), C.sizeof(_lib.DeviceInfo),
+                     C.sizeof(_lib.MicrobenchResult), C.sizeof(_lib.Template), C.sizeof(_lib.BatchItem),
+                     _lib.Result.hashes_done.offset]
+
+
+@pytest.mark.skipif(has_gpu(), reason="only meaningful on a machine without a GPU")
+def test_no_cpu_fallback_without_gpu():
+    import upow_b200
+    with pytest.raises(upow_b200.UpowError) as e:
+        upow_b200.Context(1)
+    assert e.value.code == -2
+
+
+def test_product_package_never_imports_oracle():
+    pkg = os.path.join(ROOT, "upow_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+\.*oracle", text, re.M), f
+                assert "libupow_oracle" not in text and "upow_oracle" not in text and "oracle/" not in text, f
+
+
+class _FakeResult:
+    def __init__(self, nonce, ts, hashes=1000):
+        self.nonce, self.timestamp, self.hashes_done, self.found = nonce, ts, hashes, 1
+
+
+class _FakeContext:
+    """Stands in for upow_b200.Context: answers from the oracle.  Only exercises miner.py's control flow."""
+
+    def __init__(self):
+        self.calls = []
+
+    def set_template(self, slot, prefix, prev_hash, n_int, cc):
+        self.prefix, self.prev_hash, self.n_int, self.cc = prefix, prev_hash, n_int, cc
+
+    def search_min(self, slot, start, stride, time_limit_s=0, max_rollovers=0, **kw):
+        self.calls.append((start, stride, time_limit_s))
+        tgt = self.prev_hash.hex()[-self.n_int:]
+        n = start
+        while n < 2 ** 32:
+            h = hashlib.sha256(self.prefix + n.to_bytes(4, "little")).hexdigest()
+            if h.startswith(tgt) and (self.cc == 16 or int(h[self.n_int], 16) < self.cc):
+                return 0, _FakeResult(n, O.get_timestamp(self.prefix))
+            n += stride
+        return 1, _FakeResult(0, 0)
+
+
+def test_miner_mirror_call_surface(monkeypatch, capsys, mine_block_vectors):
+    """mine_block(start, inc, params) posts the same JSON the reference posts (golden vectors)."""
+    import types
+    from upow_b200 import miner
+    posted = {}
+
+    class Resp:
+        def json(self):
+            return {"ok": True}
+
+    fake_requests = types.ModuleType("requests")
+    fake_requests.post = lambda url, json=None, timeout=None: (posted.update(json, url=url, timeout=timeout), Resp())[1]
+    monkeypatch.setitem(sys.modules, "requests", fake_requests)
+    for v in [x for x in mine_block_vectors if x["nonce"] < 700_000][:10]:
+        posted.clear()
+        ctx = _FakeContext()
+        miner.set_context(ctx)
+        monkeypatch.setattr(sys, "argv", ["miner.py", v["wallet"], "1", "http://node.example:3006"])
+        monkeypatch.setattr(miner, "timestamp", lambda ts=v["timestamp"]: ts)
+        params = {k: (dict(val) if isinstance(val, dict) else val) for k, val in v["mining_params"].items()}
+        with pytest.raises(SystemExit):
+            miner.mine_block(v["start_nonce"], v["nonce_increment"], params)
+        assert posted["block_content"] == v["block_content"], v["name"]
+        assert posted["txs"] == v["posted_txs"] and posted["block_no"] == v["posted_block_no"]
+        assert posted["url"] == "http://node.example:3006/push_block"
+        assert posted["timeout"] == 20 + int((len(v["posted_txs"]) or 1) / 3)
+        assert ctx.calls == [(v["start_nonce"], v["nonce_increment"], 90)]
+        out = capsys.readouterr().out
+        assert v["block_content"] in out and "BLOCK MINED" in out
+        if v["start_nonce"] == 0:
+            assert f"difficulty: {v['mining_params']['difficulty']}" in out
+    miner.set_context(None)
+
+
+def test_miner_mirror_exhaustion_raises_overflow(monkeypatch):
+    import types
+    from upow_b200 import miner, _lib
+
+    class Ctx(_FakeContext):
+        def search_min(self, *a, **k):
+            return _lib.UPOW_EXHAUSTED, _FakeResult(0, 0)
+
+    monkeypatch.setitem(sys.modules, "requests", types.ModuleType("requests"))
+    miner.set_context(Ctx())
+    monkeypatch.setattr(sys, "argv", ["miner.py", O.T0_ADDRESS_V1])
+    with pytest.raises(OverflowError):  # the reference: nonce.to_bytes(4, ...) at 2**32, miner.py:87
+        miner.mine_block(0, 1, O.t0_mining_params(4.0))
+    miner.set_context(None)
