@@ -139,6 +139,15 @@ int upow_sweep(upow_ctx* ctx, int slot, uint64_t nonce_lo, uint64_t nonce_hi, ui
 int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates, uint64_t max_nonce,
                       upow_batch_item* results, upow_result* stats);
 
+/* The library carries several builds of the search kernel that differ only in how the integer
+ * work is spread over the SM's alu and fma issue pipes (DESIGN.md "pipe balance"); results are
+ * identical.  Variant 0 is the plain-CUDA kernel.  The default is the fastest one measured on
+ * B200; env UPOW_VARIANT overrides it at upow_init. */
+int upow_variant_count(void);
+const char* upow_variant_name(int variant);
+int upow_get_variant(const upow_ctx* ctx);
+int upow_set_variant(upow_ctx* ctx, int variant);
+
 /* Stops a running search from another thread or a signal handler (only sets a flag; the
  * reference's equivalent is the parent terminating its workers, miner.py:155-156). */
 int upow_cancel(upow_ctx* ctx);

@@ -54,7 +54,7 @@ def host_harness():
     os.makedirs(out_dir, exist_ok=True)
     so = os.path.join(out_dir, "host_harness.so")
     src = os.path.join(ROOT, "tests", "host_harness.cpp")
-    deps = [src] + [os.path.join(ROOT, "upow_b200", "csrc", f) for f in ("template_prep.h", "sha256_core.h")]
+    deps = [src] + [os.path.join(ROOT, "upow_b200", "csrc", f) for f in ("template_prep.h", "sha256_core.h", "hot_loop.h")]
     if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so, src])
     return ctypes.CDLL(so)

@@ -5,7 +5,7 @@
 #include <stdint.h>
 #include <string.h>
 
-#include "../upow_b200/csrc/template_prep.h"
+#include "../upow_b200/csrc/hot_loop.h"
 
 using namespace upow;
 
@@ -63,6 +63,21 @@ uint32_t hh_strided_a64(const Tail* t, uint32_t nonce) {
     }
     host_rounds(st, w, 0, 64);
     return st[0];
+}
+
+// the hand-specialised hot loops of hot_loop.h (portable fallbacks of the pipe-controlled primitives)
+uint32_t hh_tuned_a64(const Tail* t, uint32_t nonce) {
+    using Tn = Tune<1, 1, 0x24, 2, 0xa, 3>;
+    Opaque q;
+    fill_opaque(&q);
+    const uint32_t H = nonce >> 16, L = nonce & 0xffff;
+    if (t->layout == LAYOUT_V1) {
+        V1Lane lane = v1_lane_setup(*t, L);
+        return v1_nonce_a64<Tn>(lane, v1_w2(H), q);
+    }
+    V2Consts u;
+    prepare_v2_consts(*t, &u);
+    return v2_nonce_a64<Tn>(u, v2_w10_from_L(L) | v2_w10_from_H(H), q);
 }
 
 int hh_prefilter(const Rule* r, uint32_t a64) { return a64 + r->sub0 < r->range0; }

@@ -50,6 +50,7 @@ def test_midstate_tail_and_hot_path(host_harness, version):
     """Tail::mid/w/pre and the PRMT word builders give hashlib's digest word 0 for every nonce shape."""
     host_harness.hh_hot_a64.restype = C.c_uint32
     host_harness.hh_strided_a64.restype = C.c_uint32
+    host_harness.hh_tuned_a64.restype = C.c_uint32
     rng = random.Random(10 + version)
     for trial in range(20):
         prefix = rng.randbytes(134 if version == 1 else 104)
@@ -68,6 +69,7 @@ def test_midstate_tail_and_hot_path(host_harness, version):
             w0 = int.from_bytes(want[:4], "big")
             assert (host_harness.hh_hot_a64(C.byref(t), nonce) + t.mid[0]) & 0xffffffff == w0
             assert (host_harness.hh_strided_a64(C.byref(t), nonce) + t.mid[0]) & 0xffffffff == w0
+            assert (host_harness.hh_tuned_a64(C.byref(t), nonce) + t.mid[0]) & 0xffffffff == w0
 
 
 def test_rule_nibble_form_matches_reference_rule(host_harness):

@@ -51,17 +51,26 @@ def parse(path):
 
 
 def hot_loop(instrs):
-    """(start, end) addresses of the largest backward branch region."""
-    best = None
+    """(start, end) of the per-nonce loop: start from the largest backward-branch region and
+    descend while it contains another loop at least half its size (the outer item loop wraps
+    the inner nonce loop)."""
+    loops = []
     for addr, ins in instrs:
-        m = re.search(r"\bBRA(?:\.\w+)*\s+(?:[!\w]+,\s*)*`?\(?\.?L?_?x?_?\w*\)?", ins)
-        if "BRA" in ins.split()[0:2] or re.match(r"(@!?U?P\d+\s+)?BRA", ins):
+        if re.match(r"(@!?U?P\d+\s+)?BRA", ins):
             t = re.search(r"0x([0-9a-f]+)", ins)
             if t:
                 tgt = int(t.group(1), 16)
-                if tgt <= addr and (best is None or addr - tgt > best[1] - best[0]):
-                    best = (tgt, addr)
-    return best
+                if tgt <= addr:
+                    loops.append((tgt, addr))
+    if not loops:
+        return None
+    cur = max(loops, key=lambda l: l[1] - l[0])
+    while True:
+        inner = [l for l in loops if l != cur and cur[0] <= l[0] and l[1] <= cur[1]
+                 and (l[1] - l[0]) * 2 >= (cur[1] - cur[0])]
+        if not inner:
+            return cur
+        cur = max(inner, key=lambda l: l[1] - l[0])
 
 
 def count(instrs, lo, hi):

@@ -18,6 +18,7 @@ EXPORTS = [
     "upow_init", "upow_destroy", "upow_device_count", "upow_get_device_info", "upow_last_error",
     "upow_set_template", "upow_search_min", "upow_sweep", "upow_search_batch", "upow_cancel",
     "upow_selftest", "upow_microbench_count", "upow_microbench", "upow_flush_l2", "upow_version",
+    "upow_variant_count", "upow_variant_name", "upow_get_variant", "upow_set_variant",
 ]
 
 
@@ -104,6 +105,10 @@ def load():
     L.upow_microbench.argtypes = [C.c_int, C.c_int, C.c_uint32, C.POINTER(MicrobenchResult)]
     L.upow_flush_l2.argtypes = [vp]
     L.upow_version.restype = C.c_char_p
+    L.upow_variant_name.argtypes = [C.c_int]
+    L.upow_variant_name.restype = C.c_char_p
+    L.upow_get_variant.argtypes = [vp]
+    L.upow_set_variant.argtypes = [vp, C.c_int]
     for name in EXPORTS:
         getattr(L, name)  # AttributeError here = header and library disagree
     _lib = L
@@ -202,6 +207,19 @@ class Context:
 
     def cancel(self):
         self._L.upow_cancel(self._h)
+
+    @property
+    def variant(self) -> int:
+        return self._L.upow_get_variant(self._h)
+
+    @variant.setter
+    def variant(self, v: int):
+        rc = self._L.upow_set_variant(self._h, v)
+        if rc != UPOW_OK:
+            raise UpowError(rc, "upow_set_variant")
+
+    def variants(self):
+        return [self._L.upow_variant_name(i).decode() for i in range(self._L.upow_variant_count())]
 
     def flush_l2(self):
         rc = self._L.upow_flush_l2(self._h)

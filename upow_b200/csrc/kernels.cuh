@@ -24,6 +24,7 @@
 
 #include "sha256_core.h"
 #include "template_prep.h"
+#include "hot_loop.h"
 
 namespace upow {
 
@@ -35,7 +36,7 @@ struct DevResult {
     unsigned long long items_done;  // completed warp items (hashes_done = items_done * 32 * hc)
     unsigned int count;             // MODE_ENUM: valid nonces seen (may exceed the capacity)
     unsigned int abort_flag;        // written by the host to stop the kernel early
-    unsigned int pad[2];
+    unsigned long long next_item;   // dynamic work queue: next unclaimed item index
     unsigned long long clk_cycles;  // clock64() span of warp 0 (SM clock = cycles / ns)
     unsigned long long clk_ns;      // %globaltimer span of the same region
 };
@@ -52,6 +53,8 @@ struct SearchArgs {
     uint32_t* out;        // MODE_ENUM: valid nonces
     uint32_t cap;
     uint32_t pad;
+    Opaque q;             // opaque 1 / 2^k operands of the pipe-controlled primitives (hot_loop.h)
+    V2Consts v2;          // host-summed schedule constants of the 108-byte layout
 };
 
 struct StridedArgs {
@@ -72,6 +75,12 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
+}
+// Claims the next item of the launch-wide queue for the calling warp (lane 0 does the atomic).
+__device__ __forceinline__ unsigned long long claim_item(unsigned long long* counter, uint32_t lane) {
+    unsigned long long item = 0;
+    if (lane == 0) item = atomicAdd(counter, 1ull);
+    return __shfl_sync(0xffffffffu, item, 0);
 }
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
     return *reinterpret_cast<const volatile unsigned long long*>(p);
@@ -130,12 +139,14 @@ template <int LAYOUT, int MODE, int NPT>
 __global__ void __launch_bounds__(256) search_kernel(const __grid_constant__ SearchArgs A) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
     uint32_t done = 0;
     unsigned long long clk0 = 0, ns0 = 0;
     if (warp == 0) { clk0 = clock64(); ns0 = global_timer_ns(); }
 
-    for (uint32_t item = warp; item < A.n_items; item += n_warps) {
+    for (;;) {
+        const unsigned long long claimed = claim_item(&A.res->next_item, lane);  // increasing order
+        if (claimed >= A.n_items) break;
+        const uint32_t item = (uint32_t)claimed;
         const uint32_t hchunk = item >> 11, lgroup = item & 2047;
         const uint32_t h0 = A.h_lo + hchunk * A.hc;
         uint32_t h_end = h0 + A.hc;
@@ -218,17 +229,73 @@ __global__ void __launch_bounds__(256) search_kernel(const __grid_constant__ Sea
     }
 }
 
+// Contiguous search, hand-specialised per layout with explicit pipe assignment (hot_loop.h).
+// Same work decomposition and hit protocol as search_kernel above; Tn selects how much of the
+// integer work is issued on the fma pipe.
+template <int LAYOUT, int MODE, class Tn, int MINB>
+__global__ void __launch_bounds__(256, MINB) search_kernel_tuned(const __grid_constant__ SearchArgs A) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    uint32_t done = 0;
+    unsigned long long clk0 = 0, ns0 = 0;
+    if (warp == 0) { clk0 = clock64(); ns0 = global_timer_ns(); }
+
+    // Items are claimed from a device-wide counter, in increasing order.  (A static split leaves
+    // the SM half empty at the end: the warp scheduler favours some warps, those finish their
+    // share early, and the stragglers then run without enough parallelism -- measured with ncu:
+    // 17 of 24 warps active on average.)
+    for (;;) {
+        const unsigned long long claimed = claim_item(&A.res->next_item, lane);
+        if (claimed >= A.n_items) break;
+        const uint32_t item = (uint32_t)claimed;
+        const uint32_t hchunk = item >> 11, lgroup = item & 2047;
+        const uint32_t h0 = A.h_lo + hchunk * A.hc;
+        uint32_t h_end = h0 + A.hc;
+        if (h_end > A.h_lo + A.h_count) h_end = A.h_lo + A.h_count;
+        bool stop = ld_volatile_u32(&A.res->abort_flag) != 0;
+        if (MODE == MODE_MIN) stop = stop || ld_volatile_u64(&A.res->best) < ((unsigned long long)h0 << 16);
+        if (__any_sync(0xffffffffu, stop)) break;
+        const uint32_t L = (lgroup << 5) | lane;
+
+        if (LAYOUT == LAYOUT_V1) {
+            const V1Lane s = v1_lane_setup(A.tail, L);
+            for (uint32_t H = h0; H < h_end; H++) {
+                const uint32_t a64 = v1_nonce_a64<Tn>(s, v1_w2(H), A.q);
+                const bool hit = addu<Tn::ADD != 0>(a64, A.rule.sub0, A.q) < A.rule.range0;
+                if (__ballot_sync(0xffffffffu, hit)) {
+                    if (hit) report_hit<MODE>(A.tail, A.rule, A.nonce_lo, A.nonce_hi, (H << 16) | L, A.res, A.out, A.cap);
+                }
+            }
+        } else {
+            const uint32_t lsw = v2_w10_from_L(L);
+            for (uint32_t H = h0; H < h_end; H++) {
+                const uint32_t a64 = v2_nonce_a64<Tn>(A.v2, lsw | v2_w10_from_H(H), A.q);
+                const bool hit = addu<Tn::ADD != 0>(a64, A.rule.sub0, A.q) < A.rule.range0;
+                if (__ballot_sync(0xffffffffu, hit)) {
+                    if (hit) report_hit<MODE>(A.tail, A.rule, A.nonce_lo, A.nonce_hi, (H << 16) | L, A.res, A.out, A.cap);
+                }
+            }
+        }
+        done++;
+    }
+    if (lane == 0 && done) atomicAdd(&A.res->items_done, (unsigned long long)done);
+    if (warp == 0 && lane == 0) {
+        A.res->clk_cycles = clock64() - clk0;
+        A.res->clk_ns = global_timer_ns() - ns0;
+    }
+}
+
 // Strided search (the reference's residue-class worker layout, miner.py:139-148):
 // nonce_i = start + i*stride.  Nothing is hoisted: all 64 rounds run per nonce from the
 // midstate, which also makes this kernel an independent cross-check of search_kernel.
 template <int LAYOUT, int MODE>
 __global__ void __launch_bounds__(256) search_strided_kernel(const __grid_constant__ StridedArgs A) {
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
     uint32_t done = 0;
-    for (uint32_t item = warp; item < A.n_items; item += n_warps) {
-        const unsigned long long i0 = (unsigned long long)item * 32u * A.ic;
+    for (;;) {
+        const unsigned long long item = claim_item(&A.res->next_item, lane);
+        if (item >= A.n_items) break;
+        const unsigned long long i0 = item * 32u * A.ic;
         bool stop = ld_volatile_u32(&A.res->abort_flag) != 0;
         if (MODE == MODE_MIN) stop = stop || ld_volatile_u64(&A.res->best) < A.start + i0 * A.stride;
         if (__any_sync(0xffffffffu, stop)) break;
@@ -288,11 +355,11 @@ struct BatchArgs {
 template <int LAYOUT>
 __global__ void __launch_bounds__(256) batch_kernel(const __grid_constant__ BatchArgs A) {
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
     const unsigned long long n_items = (unsigned long long)A.n_active * A.items_per_job;
     uint32_t done = 0;
-    for (unsigned long long item = warp; item < n_items; item += n_warps) {
+    for (;;) {
+        const unsigned long long item = claim_item(&A.res->next_item, lane);
+        if (item >= n_items) break;
         const uint32_t slot = (uint32_t)(item / A.items_per_job);
         const uint32_t rem = (uint32_t)(item - (unsigned long long)slot * A.items_per_job);
         const uint32_t hchunk = rem >> 11, lgroup = rem & 2047;

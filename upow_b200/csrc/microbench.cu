@@ -31,13 +31,28 @@ enum Op : int {
     OP_MIX_3ALU_1IMAD,    // SHF, SHF, LOP3, IMAD_ADD
     OP_MIX_SHF_IMADHI,    // 1 SHF : 1 IMAD.HI
     OP_MIX_SHF_LOP3,      // 1 SHF : 1 LOP3 (same pipe; should equal the single-op rate)
+    // ---- register-file read bandwidth: operands rotate over 8 live registers so that the
+    //      operand-reuse cache cannot help; "Nr" = distinct register reads per instruction ----
+    OP_LOP3_3R,           // lop3 a_i, a_i, a_j, a_k
+    OP_IMAD_3R,           // mad.lo a_i = a_j * a_k + a_i
+    OP_IMAD_2R_IMM,       // mad.lo a_i = a_j * imm + a_i
+    OP_IADD3_3R,          // a_i = a_i + a_j + a_k   (one IADD3 after ptxas fusion)
+    OP_MIX_LOP3_3R_IMAD_3R,     // 6 reads per pair
+    OP_MIX_LOP3_3R_IMAD_2R,     // 5 reads per pair
+    OP_MIX_SHF_1R_IMAD_3R,      // 4 reads per pair
+    OP_MIX_SHF_1R_IMAD_2R,      // 3 reads per pair
+    OP_MIX_LOP3_2R_IMAD_2R,     // 4 reads per pair (lop3 with an immediate)
+    OP_MIX_SHA_LIKE,            // 3 SHF(1r) + 2 LOP3(3r) + 4 IMAD(2r imm-one) per 9: close to the tuned round mix
     OP_COUNT
 };
 
 const char* const OP_NAMES[OP_COUNT] = {
     "IADD3", "LOP3", "SHF.rot", "SHF.shr", "PRMT", "IMAD", "IMAD.add(c[1])", "IMAD.HI", "IMAD.WIDE",
     "mix SHF+IMAD 1:1", "mix LOP3+IMAD 1:1", "mix SHF,LOP3,IMAD 2:1", "mix SHF,SHF,LOP3,IMAD 3:1",
-    "mix SHF+IMAD.HI 1:1", "mix SHF+LOP3 1:1"};
+    "mix SHF+IMAD.HI 1:1", "mix SHF+LOP3 1:1",
+    "LOP3 3 reg reads", "IMAD 3 reg reads", "IMAD 2 reg reads (imm)", "IADD3 3 reg reads",
+    "mix LOP3(3r)+IMAD(3r)", "mix LOP3(3r)+IMAD(2r)", "mix SHF(1r)+IMAD(3r)", "mix SHF(1r)+IMAD(2r)",
+    "mix LOP3(2r)+IMAD(2r)", "mix sha-like 3SHF+2LOP3+4IMAD(2r)"};
 
 struct MbArgs {
     uint32_t m;      // opaque multiplier (a power of two at run time; unknown to ptxas)
@@ -50,7 +65,7 @@ struct MbArgs {
     uint32_t* sink;
 };
 
-#define A_IADD3(x) asm volatile("add.u32 %0, %0, %1;" : "+r"(x) : "r"(b))
+#define A_IADD3(x) asm volatile("add.u32 %0, %0, %1;" : "+r"(x) : "r"(b))  /* ptxas folds repeated adds: kept only as a curiosity */
 #define A_LOP3(x) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x) : "r"(b), "r"(c))
 #define A_ROT(x) asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x))
 #define A_SHR(x) asm volatile("shf.r.clamp.b32 %0, %0, %1, 3;" : "+r"(x) : "r"(b))
@@ -61,6 +76,14 @@ struct MbArgs {
 #define A_IMADWIDE(x, y)                                                                     \
     asm volatile("{.reg .u64 t; mad.wide.u32 t, %0, %2, %3; mov.b64 {%0, %1}, t;}"           \
                  : "+r"(x), "+r"(y) : "r"(m), "l"(wide_c))
+
+// rotating-operand forms: X is updated from itself and two (one) other live accumulators
+#define R_LOP3(x, y, z) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x) : "r"(y), "r"(z))
+#define R_LOP3I(x, y) asm volatile("lop3.b32 %0, %0, %1, 0x5a5a5a5a, 0x96;" : "+r"(x) : "r"(y))
+#define R_IMAD3(x, y, z) asm volatile("mad.lo.u32 %0, %1, %2, %0;" : "+r"(x) : "r"(y), "r"(z))
+#define R_IMAD2(x, y) asm volatile("mad.lo.u32 %0, %1, 0x9e3779b1, %0;" : "+r"(x) : "r"(y))
+#define R_IADD3(x, y, z) asm volatile("{ .reg .u32 t; add.u32 t, %1, %2; add.u32 %0, %0, t; }" : "+r"(x) : "r"(y), "r"(z))
+#define R_ROT(x) asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x))
 
 // 8 chains x 4 = 32 ops per REP4 invocation
 #define REP8(OPM) OPM(a0); OPM(a1); OPM(a2); OPM(a3); OPM(a4); OPM(a5); OPM(a6); OPM(a7)
@@ -113,6 +136,66 @@ __global__ void __launch_bounds__(256) mb_kernel(const __grid_constant__ MbArgs 
                 A_ROT(a0); A_IMADHI(a1); A_ROT(a2); A_IMADHI(a3); A_ROT(a4); A_IMADHI(a5); A_ROT(a6); A_IMADHI(a7);
                 A_IMADHI(a0); A_ROT(a1); A_IMADHI(a2); A_ROT(a3); A_IMADHI(a4); A_ROT(a5); A_IMADHI(a6); A_ROT(a7);
             }
+            if (OP == OP_LOP3_3R) {
+                R_LOP3(a0, a1, a2); R_LOP3(a3, a4, a5); R_LOP3(a6, a7, a0); R_LOP3(a1, a2, a3);
+                R_LOP3(a4, a5, a6); R_LOP3(a7, a0, a1); R_LOP3(a2, a3, a4); R_LOP3(a5, a6, a7);
+                R_LOP3(a0, a3, a6); R_LOP3(a1, a4, a7); R_LOP3(a2, a5, a0); R_LOP3(a3, a6, a1);
+                R_LOP3(a4, a7, a2); R_LOP3(a5, a0, a3); R_LOP3(a6, a1, a4); R_LOP3(a7, a2, a5);
+            }
+            if (OP == OP_IMAD_3R) {
+                R_IMAD3(a0, a1, a2); R_IMAD3(a3, a4, a5); R_IMAD3(a6, a7, a0); R_IMAD3(a1, a2, a3);
+                R_IMAD3(a4, a5, a6); R_IMAD3(a7, a0, a1); R_IMAD3(a2, a3, a4); R_IMAD3(a5, a6, a7);
+                R_IMAD3(a0, a3, a6); R_IMAD3(a1, a4, a7); R_IMAD3(a2, a5, a0); R_IMAD3(a3, a6, a1);
+                R_IMAD3(a4, a7, a2); R_IMAD3(a5, a0, a3); R_IMAD3(a6, a1, a4); R_IMAD3(a7, a2, a5);
+            }
+            if (OP == OP_IMAD_2R_IMM) {
+                R_IMAD2(a0, a1); R_IMAD2(a2, a3); R_IMAD2(a4, a5); R_IMAD2(a6, a7);
+                R_IMAD2(a1, a2); R_IMAD2(a3, a4); R_IMAD2(a5, a6); R_IMAD2(a7, a0);
+                R_IMAD2(a0, a3); R_IMAD2(a2, a5); R_IMAD2(a4, a7); R_IMAD2(a6, a1);
+                R_IMAD2(a1, a4); R_IMAD2(a3, a6); R_IMAD2(a5, a0); R_IMAD2(a7, a2);
+            }
+            if (OP == OP_IADD3_3R) {
+                R_IADD3(a0, a1, a2); R_IADD3(a3, a4, a5); R_IADD3(a6, a7, a0); R_IADD3(a1, a2, a3);
+                R_IADD3(a4, a5, a6); R_IADD3(a7, a0, a1); R_IADD3(a2, a3, a4); R_IADD3(a5, a6, a7);
+                R_IADD3(a0, a3, a6); R_IADD3(a1, a4, a7); R_IADD3(a2, a5, a0); R_IADD3(a3, a6, a1);
+                R_IADD3(a4, a7, a2); R_IADD3(a5, a0, a3); R_IADD3(a6, a1, a4); R_IADD3(a7, a2, a5);
+            }
+            if (OP == OP_MIX_LOP3_3R_IMAD_3R) {
+                R_LOP3(a0, a1, a2); R_IMAD3(a3, a4, a5); R_LOP3(a6, a7, a0); R_IMAD3(a1, a2, a3);
+                R_LOP3(a4, a5, a6); R_IMAD3(a7, a0, a1); R_LOP3(a2, a3, a4); R_IMAD3(a5, a6, a7);
+                R_LOP3(a0, a3, a6); R_IMAD3(a1, a4, a7); R_LOP3(a2, a5, a0); R_IMAD3(a3, a6, a1);
+                R_LOP3(a4, a7, a2); R_IMAD3(a5, a0, a3); R_LOP3(a6, a1, a4); R_IMAD3(a7, a2, a5);
+            }
+            if (OP == OP_MIX_LOP3_3R_IMAD_2R) {
+                R_LOP3(a0, a1, a2); R_IMAD2(a3, a4); R_LOP3(a6, a7, a0); R_IMAD2(a1, a2);
+                R_LOP3(a4, a5, a6); R_IMAD2(a7, a0); R_LOP3(a2, a3, a4); R_IMAD2(a5, a6);
+                R_LOP3(a0, a3, a6); R_IMAD2(a1, a4); R_LOP3(a2, a5, a0); R_IMAD2(a3, a6);
+                R_LOP3(a4, a7, a2); R_IMAD2(a5, a0); R_LOP3(a6, a1, a4); R_IMAD2(a7, a2);
+            }
+            if (OP == OP_MIX_SHF_1R_IMAD_3R) {
+                R_ROT(a0); R_IMAD3(a3, a4, a5); R_ROT(a6); R_IMAD3(a1, a2, a3);
+                R_ROT(a4); R_IMAD3(a7, a0, a1); R_ROT(a2); R_IMAD3(a5, a6, a7);
+                R_ROT(a0); R_IMAD3(a1, a4, a7); R_ROT(a2); R_IMAD3(a3, a6, a1);
+                R_ROT(a4); R_IMAD3(a5, a0, a3); R_ROT(a6); R_IMAD3(a7, a2, a5);
+            }
+            if (OP == OP_MIX_SHF_1R_IMAD_2R) {
+                R_ROT(a0); R_IMAD2(a3, a4); R_ROT(a6); R_IMAD2(a1, a2);
+                R_ROT(a4); R_IMAD2(a7, a0); R_ROT(a2); R_IMAD2(a5, a6);
+                R_ROT(a0); R_IMAD2(a1, a4); R_ROT(a2); R_IMAD2(a3, a6);
+                R_ROT(a4); R_IMAD2(a5, a0); R_ROT(a6); R_IMAD2(a7, a2);
+            }
+            if (OP == OP_MIX_LOP3_2R_IMAD_2R) {
+                R_LOP3I(a0, a1); R_IMAD2(a3, a4); R_LOP3I(a6, a7); R_IMAD2(a1, a2);
+                R_LOP3I(a4, a5); R_IMAD2(a7, a0); R_LOP3I(a2, a3); R_IMAD2(a5, a6);
+                R_LOP3I(a0, a3); R_IMAD2(a1, a4); R_LOP3I(a2, a5); R_IMAD2(a3, a6);
+                R_LOP3I(a4, a7); R_IMAD2(a5, a0); R_LOP3I(a6, a1); R_IMAD2(a7, a2);
+            }
+            if (OP == OP_MIX_SHA_LIKE) {  // 18 ops: 6 SHF + 4 LOP3(3r) + 8 IMAD(2r)
+                R_ROT(a0); R_IMAD2(a1, a2); R_ROT(a3); R_IMAD2(a4, a5); R_ROT(a6); R_IMAD2(a7, a0);
+                R_LOP3(a0, a3, a6); R_IMAD2(a2, a1); R_LOP3(a1, a4, a7); R_IMAD2(a5, a3);
+                R_ROT(a2); R_IMAD2(a6, a4); R_ROT(a5); R_IMAD2(a0, a7); R_ROT(a7); R_IMAD2(a3, a1);
+                R_LOP3(a2, a5, a7); R_LOP3(a4, a6, a0);
+            }
             if (OP == OP_MIX_SHF_LOP3) {
                 A_ROT(a0); A_LOP3(a1); A_ROT(a2); A_LOP3(a3); A_ROT(a4); A_LOP3(a5); A_ROT(a6); A_LOP3(a7);
                 A_LOP3(a0); A_ROT(a1); A_LOP3(a2); A_ROT(a3); A_LOP3(a4); A_ROT(a5); A_LOP3(a6); A_ROT(a7);
@@ -132,12 +215,17 @@ __global__ void __launch_bounds__(256) mb_kernel(const __grid_constant__ MbArgs 
 int ops_per_trip(int op) {
     if (op == OP_MIX_2ALU_1IMAD) return 16 * 18;
     if (op == OP_MIX_3ALU_1IMAD) return 16 * 16;
+    if (op == OP_MIX_SHA_LIKE) return 16 * 18;
     return 256;
 }
 int fma_ops_per_trip(int op) {
     switch (op) {
         case OP_IMAD: case OP_IMAD_ADD: case OP_IMAD_HI: case OP_IMAD_WIDE: return 256;
         case OP_MIX_SHF_IMAD: case OP_MIX_LOP3_IMAD: case OP_MIX_SHF_IMADHI: return 128;
+        case OP_IMAD_3R: case OP_IMAD_2R_IMM: return 256;
+        case OP_MIX_LOP3_3R_IMAD_3R: case OP_MIX_LOP3_3R_IMAD_2R: case OP_MIX_SHF_1R_IMAD_3R:
+        case OP_MIX_SHF_1R_IMAD_2R: case OP_MIX_LOP3_2R_IMAD_2R: return 128;
+        case OP_MIX_SHA_LIKE: return 16 * 8;
         case OP_MIX_2ALU_1IMAD: return 16 * 6;
         case OP_MIX_3ALU_1IMAD: return 16 * 4;
         default: return 0;

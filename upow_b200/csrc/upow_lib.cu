@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -45,6 +46,7 @@ struct Device {
     int id = -1;
     int sm_count = 0;
     int grid_blocks = 0;
+    int variant_grid[16] = {0};
     cudaDeviceProp prop;
     cudaStream_t stream = nullptr, ctrl = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -73,6 +75,7 @@ struct upow_ctx {
     std::mutex err_mu;
     std::string err;
     std::mutex api_mu;  // one search at a time per context
+    int variant = -1;   // index into VARIANTS
 };
 
 namespace {
@@ -171,12 +174,39 @@ struct TileOut {
     int status = 0;      // 0, UPOW_CANCELLED, UPOW_EXHAUSTED(deadline)
 };
 
-template <int MODE>
-cudaError_t launch_search(const Device& d, const SearchArgs& a) {
-    if (a.tail.layout == LAYOUT_V1)
-        search_kernel<LAYOUT_V1, MODE, 1><<<d.grid_blocks, 256, 0, d.stream>>>(a);
-    else
-        search_kernel<LAYOUT_V2, MODE, 1><<<d.grid_blocks, 256, 0, d.stream>>>(a);
+// ---- kernel variants -------------------------------------------------------------------
+// Variant 0 is the plain-CUDA kernel (compiler-chosen pipes); the others are the
+// hand-specialised loops of hot_loop.h with different shares of work on the fma pipe.
+typedef void (*SearchFn)(const SearchArgs);
+struct Variant {
+    const char* name;
+    SearchFn fn[2][2];  // [layout-1][mode]
+};
+#define UPOW_PLAIN_VARIANT(NAME)                                                                     \
+    { NAME, { { search_kernel<LAYOUT_V1, MODE_MIN, 1>, search_kernel<LAYOUT_V1, MODE_ENUM, 1> },      \
+              { search_kernel<LAYOUT_V2, MODE_MIN, 1>, search_kernel<LAYOUT_V2, MODE_ENUM, 1> } } }
+#define UPOW_TUNED_VARIANT(NAME, TN, MINB)                                                           \
+    { NAME, { { search_kernel_tuned<LAYOUT_V1, MODE_MIN, TN, MINB>, search_kernel_tuned<LAYOUT_V1, MODE_ENUM, TN, MINB> }, \
+              { search_kernel_tuned<LAYOUT_V2, MODE_MIN, TN, MINB>, search_kernel_tuned<LAYOUT_V2, MODE_ENUM, TN, MINB> } } }
+#define TN(...) Tune<__VA_ARGS__>
+const Variant VARIANTS[] = {
+    UPOW_PLAIN_VARIANT("plain: nvcc-chosen pipes"),
+    UPOW_TUNED_VARIANT("add+shr on fma, 3 blocks/SM", TN(1, 1, 0, 0, 0, 0), 3),
+    UPOW_TUNED_VARIANT("add+shr on fma, 4 blocks/SM", TN(1, 1, 0, 0, 0, 0), 4),
+    UPOW_TUNED_VARIANT("add+shr+rot25 on 1/4 rounds", TN(1, 1, 4, 1, 0, 0), 3),
+    UPOW_TUNED_VARIANT("add+shr+rot25 on 2/4 rounds", TN(1, 1, 4, 2, 0, 0), 3),
+    UPOW_TUNED_VARIANT("add+shr+rot25 on all rounds", TN(1, 1, 4, 4, 0, 0), 3),
+    UPOW_TUNED_VARIANT("add only on fma", TN(1, 0, 0, 0, 0, 0), 3),
+    UPOW_TUNED_VARIANT("add+shr, 7-add rounds", TN(1, 1, 0, 0, 0, 0, 0), 3),
+    UPOW_TUNED_VARIANT("add only, 7-add rounds", TN(1, 0, 0, 0, 0, 0, 0), 3),
+};
+constexpr int N_VARIANTS = sizeof(VARIANTS) / sizeof(VARIANTS[0]);
+constexpr int DEFAULT_VARIANT = 8;
+
+cudaError_t launch_search(const Device& d, const SearchArgs& a, int mode, int variant) {
+    SearchFn fn = VARIANTS[variant].fn[a.tail.layout == LAYOUT_V1 ? 0 : 1][mode == MODE_MIN ? 0 : 1];
+    int grid = d.variant_grid[variant];
+    fn<<<grid, 256, 0, d.stream>>>(a);
     return cudaGetLastError();
 }
 template <int MODE>
@@ -188,10 +218,22 @@ cudaError_t launch_strided(const Device& d, const StridedArgs& a) {
     return cudaGetLastError();
 }
 
+// persistent grid of every variant: SM count x resident blocks per SM of its v1 ENUM kernel
+int init_variant_grids(upow_ctx* ctx, Device& d) {
+    static_assert(N_VARIANTS <= 16, "variant_grid too small");
+    for (int v = 0; v < N_VARIANTS; v++) {
+        int per_sm = 0;
+        CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, VARIANTS[v].fn[0][1], 256, 0));
+        if (per_sm < 1) per_sm = 1;
+        d.variant_grid[v] = d.sm_count * per_sm;
+    }
+    return UPOW_OK;
+}
+
 // One launch over the contiguous nonce range [lo, hi) of one (template, timestamp).
 // MODE_ENUM copies up to out_cap nonces into out_host (unsorted).
 int run_contiguous(upow_ctx* ctx, Device& d, const Tail& tail, const Rule& rule, uint64_t lo, uint64_t hi, int mode,
-                   double deadline, TileOut* out, uint32_t* out_host, uint64_t out_cap) {
+                   double deadline, TileOut* out, std::vector<uint32_t>* out_host) {
     CU_TRY(ctx, cudaSetDevice(d.id));
     SearchArgs a;
     memset(&a, 0, sizeof a);
@@ -204,20 +246,22 @@ int run_contiguous(upow_ctx* ctx, Device& d, const Tail& tail, const Rule& rule,
     a.h_count = h_hi - a.h_lo;
     // items of up to 64 H values; small ranges get smaller items so every warp has work
     uint32_t hc = 64;
-    const uint32_t n_warps = d.grid_blocks * 8;
+    const uint32_t n_warps = d.variant_grid[ctx->variant] * 8;
     while (hc > 1 && (uint64_t)((a.h_count + hc - 1) / hc) * 2048 < 4ull * n_warps) hc >>= 1;
     a.hc = hc;
     a.n_items = ((a.h_count + hc - 1) / hc) * 2048;
     a.res = d.d_res;
     a.out = d.d_out;
     a.cap = ENUM_CAP;
+    fill_opaque(&a.q);
+    if (tail.layout == LAYOUT_V2) prepare_v2_consts(tail, &a.v2);
     DevResult init;
     memset(&init, 0, sizeof init);
     init.best = ~0ull;
     *d.h_res = init;
     CU_TRY(ctx, cudaMemcpyAsync(d.d_res, d.h_res, sizeof(DevResult), cudaMemcpyHostToDevice, d.stream));
     CU_TRY(ctx, cudaEventRecord(d.ev0, d.stream));
-    CU_TRY(ctx, mode == MODE_MIN ? launch_search<MODE_MIN>(d, a) : launch_search<MODE_ENUM>(d, a));
+    CU_TRY(ctx, launch_search(d, a, mode, ctx->variant));
     CU_TRY(ctx, cudaEventRecord(d.ev1, d.stream));
     int st = wait_event(ctx, d, d.ev1, deadline);
     if (st < 0) return st;
@@ -233,8 +277,9 @@ int run_contiguous(upow_ctx* ctx, Device& d, const Tail& tail, const Rule& rule,
     out->count = d.h_res->count;
     out->sm_mhz = d.h_res->clk_ns ? (double)d.h_res->clk_cycles / (double)d.h_res->clk_ns * 1000.0 : 0.0;
     if (mode == MODE_ENUM && out_host) {
-        uint64_t n = std::min<uint64_t>(std::min<uint64_t>(out->count, ENUM_CAP), out_cap);
-        if (n) CU_TRY(ctx, cudaMemcpy(out_host, d.d_out, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+        const uint64_t n = std::min<uint64_t>(out->count, ENUM_CAP);
+        out_host->resize(n);
+        if (n) CU_TRY(ctx, cudaMemcpy(out_host->data(), d.d_out, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
     }
     return UPOW_OK;
 }
@@ -352,11 +397,17 @@ extern "C" int upow_init(int n_devices, const int* device_ids, upow_ctx** out_ct
             return UPOW_E_ARG;
         }
         int rc = init_device(ctx, ctx->devs[i], id);
+        if (rc == UPOW_OK) rc = init_variant_grids(ctx, ctx->devs[i]);
         if (rc != UPOW_OK) {
             set_err(nullptr, ctx->err);
             upow_destroy(ctx);
             return rc;
         }
+    }
+    ctx->variant = DEFAULT_VARIANT;
+    if (const char* v = getenv("UPOW_VARIANT")) {
+        int k = atoi(v);
+        if (k >= 0 && k < N_VARIANTS) ctx->variant = k;
     }
     *out_ctx = ctx;
     return UPOW_OK;
@@ -375,13 +426,13 @@ extern "C" int upow_get_device_info(const upow_ctx* ctx, int index, upow_device_
     if (!ctx || !out || index < 0 || index >= (int)ctx->devs.size()) return UPOW_E_ARG;
     const Device& d = ctx->devs[index];
     memset(out, 0, sizeof *out);
-    snprintf(out->name, sizeof out->name, "%s", d.prop.name);
+    memcpy(out->name, d.prop.name, sizeof out->name - 1);
     out->device_id = d.id;
     out->sm_count = d.sm_count;
     out->cc_major = d.prop.major;
     out->cc_minor = d.prop.minor;
     out->max_sm_clock_khz = d.prop.clockRate;
-    out->search_grid_blocks = d.grid_blocks;
+    out->search_grid_blocks = d.variant_grid[ctx->variant];
     out->total_mem = d.prop.totalGlobalMem;
     return UPOW_OK;
 }
@@ -408,6 +459,16 @@ extern "C" int upow_set_template(upow_ctx* ctx, int slot, const uint8_t* prefix,
     }
     std::lock_guard<std::mutex> g(ctx->api_mu);
     ctx->slots[slot] = s;
+    return UPOW_OK;
+}
+
+extern "C" int upow_variant_count(void) { return N_VARIANTS; }
+extern "C" const char* upow_variant_name(int v) { return v >= 0 && v < N_VARIANTS ? VARIANTS[v].name : ""; }
+extern "C" int upow_get_variant(const upow_ctx* ctx) { return ctx ? ctx->variant : UPOW_E_ARG; }
+extern "C" int upow_set_variant(upow_ctx* ctx, int v) {
+    if (!ctx || v < 0 || v >= N_VARIANTS) return UPOW_E_ARG;
+    std::lock_guard<std::mutex> g(ctx->api_mu);
+    ctx->variant = v;
     return UPOW_OK;
 }
 
@@ -492,7 +553,7 @@ extern "C" int upow_search_min(upow_ctx* ctx, int slot, uint64_t start_nonce, ui
                 if (contiguous) {
                     const uint64_t lo = std::max<uint64_t>(start_nonce, (first_tile + k) * tile);
                     const uint64_t hi = std::min<uint64_t>(max_nonce, (first_tile + k + 1) * tile);
-                    rc = run_contiguous(ctx, d, p.tail, p.rule, lo, hi, MODE_MIN, deadline, &o, nullptr, 0);
+                    rc = run_contiguous(ctx, d, p.tail, p.rule, lo, hi, MODE_MIN, deadline, &o, nullptr);
                 } else {
                     const uint64_t s_lo = k * tile, s_hi = std::min<uint64_t>(units_per_ts, (k + 1) * tile);
                     rc = run_strided(ctx, d, p.tail, p.rule, start_nonce, stride, s_lo, s_hi, deadline, &o);
@@ -584,10 +645,8 @@ extern "C" int upow_sweep(upow_ctx* ctx, int slot, uint64_t nonce_lo, uint64_t n
         std::vector<int> rcs(n_dev, UPOW_OK);
         auto worker = [&](int di) {
             if (cut[di] >= cut[di + 1]) return;
-            parts[di].resize(ENUM_CAP);
             rcs[di] = run_contiguous(ctx, ctx->devs[di], p.tail, p.rule, cut[di], cut[di + 1], MODE_ENUM, 0, &outs[di],
-                                     parts[di].data(), ENUM_CAP);
-            parts[di].resize(std::min<uint64_t>(outs[di].count, ENUM_CAP));
+                                     &parts[di]);
         };
         if (n_dev == 1) worker(0);
         else {
@@ -704,6 +763,8 @@ int run_batch_on_device(upow_ctx* ctx, Device& d, const std::vector<BatchJob>& j
         CU_TRY(ctx, cudaMemcpyAsync(d.d_active, active.data(), sizeof(uint32_t) * active.size(), cudaMemcpyHostToDevice, d.stream));
         CU_TRY(ctx, cudaEventRecord(d.ev0, d.stream));
         if (has_v1) { batch_kernel<LAYOUT_V1><<<d.grid_blocks, 256, 0, d.stream>>>(a); (*launches)++; }
+        if (has_v1 && has_v2)  // both launches walk the same item list: rewind the queue in between
+            CU_TRY(ctx, cudaMemsetAsync(&d.d_res->next_item, 0, sizeof(unsigned long long), d.stream));
         if (has_v2) { batch_kernel<LAYOUT_V2><<<d.grid_blocks, 256, 0, d.stream>>>(a); (*launches)++; }
         CU_TRY(ctx, cudaGetLastError());
         CU_TRY(ctx, cudaEventRecord(d.ev1, d.stream));
