@@ -148,6 +148,27 @@ const char* upow_variant_name(int variant);
 int upow_get_variant(const upow_ctx* ctx);
 int upow_set_variant(upow_ctx* ctx, int variant);
 
+/* No counterpart in the reference.  The sweep of upow_sweep for callers that must not allocate:
+ * a host whose own arena already owns all GPU memory, a caller that cannot take the device-wide
+ * stall of cudaMalloc/cudaFree, code where creating streams, events or buffers is off limits.
+ * Needs no upow_ctx.  The device scratch (work queue, hit counter, hit buffer) is a fixed static
+ * array of UPOW_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit, so:
+ *   - cap may not exceed UPOW_NOALLOC_MAX_HITS (UPOW_E_ARG otherwise);
+ *   - all calls on a device share the array: the library serialises its own calls per device and
+ *     runs them synchronously on the legacy default stream, and clears the control block at the
+ *     start of each call; GPU work from elsewhere that overlaps a call on the same array races;
+ *   - the first call on each device resolves the array's device address and uploads constants:
+ *     issue it before any stream capture starts.
+ * Calls no cudaMalloc/cudaFree, creates no stream or event.  Output: valid nonces of
+ * [nonce_lo, nonce_hi), sorted ascending; *out_count is the true count; UPOW_E_OVERFLOW if it exceeds
+ * cap.  Error text: upow_noalloc_last_error(). */
+#define UPOW_NOALLOC_MAX_HITS 65536u
+#define UPOW_NOALLOC_SCRATCH_BYTES (256u + 4u * UPOW_NOALLOC_MAX_HITS)
+int upow_sweep_noalloc(int device, const uint8_t* prefix, int prefix_len, const uint8_t* prev_hash32, int n_int,
+                       int charset_count, uint64_t nonce_lo, uint64_t nonce_hi, uint32_t* out_nonces, uint64_t cap,
+                       uint64_t* out_count);
+const char* upow_noalloc_last_error(void);
+
 /* Stops a running search from another thread or a signal handler (only sets a flag; the
  * reference's equivalent is the parent terminating its workers, miner.py:155-156). */
 int upow_cancel(upow_ctx* ctx);

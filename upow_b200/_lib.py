@@ -19,7 +19,9 @@ EXPORTS = [
     "upow_set_template", "upow_search_min", "upow_sweep", "upow_search_batch", "upow_cancel",
     "upow_selftest", "upow_microbench_count", "upow_microbench", "upow_flush_l2", "upow_version",
     "upow_variant_count", "upow_variant_name", "upow_get_variant", "upow_set_variant",
+    "upow_sweep_noalloc", "upow_noalloc_last_error",
 ]
+NOALLOC_MAX_HITS = 65536
 
 
 class UpowError(RuntimeError):
@@ -107,6 +109,9 @@ def load():
     L.upow_version.restype = C.c_char_p
     L.upow_variant_name.argtypes = [C.c_int]
     L.upow_variant_name.restype = C.c_char_p
+    L.upow_sweep_noalloc.argtypes = [C.c_int, u8p, C.c_int, u8p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, u32p,
+                                     C.c_uint64, u64p]
+    L.upow_noalloc_last_error.restype = C.c_char_p
     L.upow_get_variant.argtypes = [vp]
     L.upow_set_variant.argtypes = [vp, C.c_int]
     for name in EXPORTS:
@@ -225,6 +230,20 @@ class Context:
         rc = self._L.upow_flush_l2(self._h)
         if rc != UPOW_OK:
             raise UpowError(rc, "upow_flush_l2", self._err())
+
+
+def sweep_noalloc(device: int, prefix: bytes, prev_hash: bytes, n_int: int, charset_count: int, nonce_lo: int,
+                  nonce_hi: int, cap: int = NOALLOC_MAX_HITS):
+    """upow_sweep_noalloc: sweep without any device allocation (for hosts that may not allocate; see the header).
+    Returns the sorted valid nonces.  The output buffer here is ordinary host memory owned by ctypes."""
+    L = load()
+    buf = (C.c_uint32 * max(cap, 1))()
+    count = C.c_uint64(0)
+    rc = L.upow_sweep_noalloc(device, bytes(prefix), len(prefix), bytes(prev_hash), n_int, charset_count, nonce_lo,
+                              nonce_hi, buf, cap, C.byref(count))
+    if rc != UPOW_OK:
+        raise UpowError(rc, "upow_sweep_noalloc", (L.upow_noalloc_last_error() or b"").decode())
+    return list(buf[: count.value])
 
 
 def selftest(device: int = 0) -> int:
