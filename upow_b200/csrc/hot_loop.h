@@ -49,9 +49,10 @@ inline void fill_opaque(Opaque* q) {
 //        applied on words with (t & 3) < SQ
 //   CH   1: Sigma1(e) is added separately into the new e and the new a (8 additions per round,
 //        one-add dependency on Sigma1); 0: T1 is formed first (7 additions, longer chain)
-template <int ADD_, int SHR_, int RR_, int RQ_, int SR_, int SQ_, int CH_ = 1>
+//   SHR  0: SHF; 1: IMAD.WIDE (high half); 2: IMAD.HI -- on schedule words with (t & 3) < SHRQ
+template <int ADD_, int SHR_, int RR_, int RQ_, int SR_, int SQ_, int CH_ = 1, int SHRQ_ = 4>
 struct Tune {
-    static constexpr int ADD = ADD_, SHR = SHR_, RR = RR_, RQ = RQ_, SR = SR_, SQ = SQ_, CH = CH_;
+    static constexpr int ADD = ADD_, SHR = SHR_, RR = RR_, RQ = RQ_, SR = SR_, SQ = SQ_, CH = CH_, SHRQ = SHRQ_;
 };
 
 // ---- pipe-controlled primitives ---------------------------------------------------------
@@ -93,10 +94,15 @@ UPOW_HD uint32_t addk(uint32_t a, const Opaque& q) {
     (void)q;
     return a + K;
 }
-template <bool FMA, int N>
+template <int FMA, int N>
 UPOW_HD uint32_t shr_n(uint32_t x, const Opaque& q) {
 #if UPOW_DEVICE_CODE
-    if (FMA) {
+    if (FMA == 2) {  // IMAD.HI: half issue rate on the fma pipe, but one destination register
+        uint32_t hi;
+        asm("mul.hi.u32 %0, %1, %2;" : "=r"(hi) : "r"(x), "r"(q.m[N]));
+        return hi;
+    }
+    if (FMA == 1) {
         uint32_t hi;
         asm("{ .reg .b64 t; .reg .b32 lo; mul.wide.u32 t, %1, %2; mov.b64 {lo, %0}, t; }"
             : "=r"(hi) : "r"(x), "r"(q.m[N]));
@@ -136,13 +142,13 @@ template <class Tn, int T>
 UPOW_HD uint32_t sig0(uint32_t x, const Opaque& q) {
     constexpr bool on = (T & 3) < Tn::SQ;
     return xor3(rotr_n<on && (Tn::SR & 1), 7>(x, q), rotr_n<on && (Tn::SR & 2), 18>(x, q),
-                shr_n<Tn::SHR != 0, 3>(x, q));
+                shr_n<(((T & 3) < Tn::SHRQ) ? Tn::SHR : 0), 3>(x, q));
 }
 template <class Tn, int T>
 UPOW_HD uint32_t sig1(uint32_t x, const Opaque& q) {
     constexpr bool on = (T & 3) < Tn::SQ;
     return xor3(rotr_n<on && (Tn::SR & 4), 17>(x, q), rotr_n<on && (Tn::SR & 8), 19>(x, q),
-                shr_n<Tn::SHR != 0, 10>(x, q));
+                shr_n<(((T & 3) < Tn::SHRQ) ? Tn::SHR : 0), 10>(x, q));
 }
 
 // One round.  `t_hk` = h + K[t] + W[t] already summed (the caller knows whether that is a

@@ -350,10 +350,13 @@ struct BatchArgs {
     uint32_t h_lo, h_count, hc;   // this round covers H in [h_lo, h_lo + h_count)
     uint32_t items_per_job;       // ceil(h_count / hc) * 2048
     uint32_t pad;
+    Opaque q;                     // see hot_loop.h
 };
 
+using BatchTune = Tune<1, 0, 0, 0, 0, 0, 0>;   // same pipe assignment as the default search variant
+
 template <int LAYOUT>
-__global__ void __launch_bounds__(256) batch_kernel(const __grid_constant__ BatchArgs A) {
+__global__ void __launch_bounds__(256, 3) batch_kernel(const __grid_constant__ BatchArgs A) {
     const uint32_t lane = threadIdx.x & 31;
     const unsigned long long n_items = (unsigned long long)A.n_active * A.items_per_job;
     uint32_t done = 0;
@@ -376,22 +379,12 @@ __global__ void __launch_bounds__(256) batch_kernel(const __grid_constant__ Batc
         uint32_t a = job.tail.pre[0], b = job.tail.pre[1], c = job.tail.pre[2], d = job.tail.pre[3];
         uint32_t e = job.tail.pre[4], f = job.tail.pre[5], g = job.tail.pre[6], h = job.tail.pre[7];
         if (LAYOUT == LAYOUT_V1) {
-            const uint32_t w0 = job.tail.w[0];
-            const uint32_t w1 = job.tail.w[1] | v1_w1_bits(L);
-            {
-                uint32_t t1 = h + big_sigma1(e) + ch(e, f, g) + (Kc(1) + w1);
-                uint32_t t2 = big_sigma0(a) + maj(a, b, c);
-                h = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
-            }
+            // the 138-byte layout runs the hand-specialised loop of hot_loop.h; the per-template words
+            // come from the job table instead of the constant bank, otherwise identical to search_kernel_tuned
+            const V1Lane s = v1_lane_setup(job.tail, L);
             for (uint32_t H = h0; H < h_end; H++) {
-                uint32_t w[16];
-                w[0] = w0; w[1] = w1;
-                w[2] = v1_w2(H);
-#pragma unroll
-                for (int i = 3; i < 15; i++) w[i] = 0u;
-                w[15] = 138u * 8u;
-                const uint32_t a64 = tail_rounds_a64<2>(a, b, c, d, e, f, g, h, w);
-                const bool hit = a64 + sub0 < range0;
+                const uint32_t a64 = v1_nonce_a64<BatchTune>(s, v1_w2(H), A.q);
+                const bool hit = add2<true>(a64, sub0, A.q) < range0;
                 if (__ballot_sync(0xffffffffu, hit)) {
                     if (hit) {
                         const uint32_t nonce = (H << 16) | L;

@@ -47,6 +47,7 @@ struct Device {
     int sm_count = 0;
     int grid_blocks = 0;
     int variant_grid[16] = {0};
+    int batch_grid = 0;
     cudaDeviceProp prop;
     cudaStream_t stream = nullptr, ctrl = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -199,6 +200,10 @@ const Variant VARIANTS[] = {
     UPOW_TUNED_VARIANT("add only on fma", TN(1, 0, 0, 0, 0, 0), 3),
     UPOW_TUNED_VARIANT("add+shr, 7-add rounds", TN(1, 1, 0, 0, 0, 0, 0), 3),
     UPOW_TUNED_VARIANT("add only, 7-add rounds", TN(1, 0, 0, 0, 0, 0, 0), 3),
+    UPOW_TUNED_VARIANT("add, 7-add, shr via IMAD.HI", TN(1, 2, 0, 0, 0, 0, 0), 3),
+    UPOW_TUNED_VARIANT("add, 7-add, shr via IMAD.HI on 2/4 words", TN(1, 2, 0, 0, 0, 0, 0, 2), 3),
+    UPOW_TUNED_VARIANT("add, 7-add, shr via IMAD.WIDE on 2/4 words", TN(1, 1, 0, 0, 0, 0, 0, 2), 3),
+    UPOW_TUNED_VARIANT("add only, 7-add rounds, 4 blocks/SM", TN(1, 0, 0, 0, 0, 0, 0), 4),
 };
 constexpr int N_VARIANTS = sizeof(VARIANTS) / sizeof(VARIANTS[0]);
 constexpr int DEFAULT_VARIANT = 8;
@@ -227,6 +232,9 @@ int init_variant_grids(upow_ctx* ctx, Device& d) {
         if (per_sm < 1) per_sm = 1;
         d.variant_grid[v] = d.sm_count * per_sm;
     }
+    int per_sm = 0;
+    CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, batch_kernel<LAYOUT_V1>, 256, 0));
+    d.batch_grid = d.sm_count * (per_sm < 1 ? 1 : per_sm);
     return UPOW_OK;
 }
 
@@ -725,7 +733,7 @@ int run_batch_on_device(upow_ctx* ctx, Device& d, const std::vector<BatchJob>& j
     std::vector<uint32_t> active(n);
     for (uint32_t i = 0; i < n; i++) active[i] = i;
     std::vector<unsigned long long> best(n, ~0ull);
-    const uint32_t n_warps = d.grid_blocks * 8;
+    const uint32_t n_warps = d.batch_grid * 8;
     const uint32_t h_total = (uint32_t)((max_nonce + 0xffff) >> 16);
     // expected work per template from its rule: 16^n_target * 16/charset
     uint32_t h_done = 0;
@@ -755,6 +763,7 @@ int run_batch_on_device(upow_ctx* ctx, Device& d, const std::vector<BatchJob>& j
         a.n_active = (uint32_t)active.size();
         a.h_lo = h_done; a.h_count = (uint32_t)h_round; a.hc = hc;
         a.items_per_job = (uint32_t)((h_round + hc - 1) / hc) * 2048;
+        fill_opaque(&a.q);
         DevResult init;
         memset(&init, 0, sizeof init);
         init.best = ~0ull;
@@ -762,10 +771,10 @@ int run_batch_on_device(upow_ctx* ctx, Device& d, const std::vector<BatchJob>& j
         CU_TRY(ctx, cudaMemcpyAsync(d.d_res, d.h_res, sizeof(DevResult), cudaMemcpyHostToDevice, d.stream));
         CU_TRY(ctx, cudaMemcpyAsync(d.d_active, active.data(), sizeof(uint32_t) * active.size(), cudaMemcpyHostToDevice, d.stream));
         CU_TRY(ctx, cudaEventRecord(d.ev0, d.stream));
-        if (has_v1) { batch_kernel<LAYOUT_V1><<<d.grid_blocks, 256, 0, d.stream>>>(a); (*launches)++; }
+        if (has_v1) { batch_kernel<LAYOUT_V1><<<d.batch_grid, 256, 0, d.stream>>>(a); (*launches)++; }
         if (has_v1 && has_v2)  // both launches walk the same item list: rewind the queue in between
             CU_TRY(ctx, cudaMemsetAsync(&d.d_res->next_item, 0, sizeof(unsigned long long), d.stream));
-        if (has_v2) { batch_kernel<LAYOUT_V2><<<d.grid_blocks, 256, 0, d.stream>>>(a); (*launches)++; }
+        if (has_v2) { batch_kernel<LAYOUT_V2><<<d.batch_grid, 256, 0, d.stream>>>(a); (*launches)++; }
         CU_TRY(ctx, cudaGetLastError());
         CU_TRY(ctx, cudaEventRecord(d.ev1, d.stream));
         int st = wait_event(ctx, d, d.ev1, 0);
