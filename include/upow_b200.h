@@ -139,6 +139,16 @@ int upow_sweep(upow_ctx* ctx, int slot, uint64_t nonce_lo, uint64_t nonce_hi, ui
 int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates, uint64_t max_nonce,
                       upow_batch_item* results, upow_result* stats);
 
+/* The first success over many templates: every template advances through the nonce space in equal
+ * rounds; the call returns after the earliest round in which any template has a valid nonce, with
+ * the lowest template index among that round's finds (so the answer does not depend on the number
+ * of GPUs) and that template's minimum nonce.  This is what a miner wants when one template's 2^32
+ * nonces per second are not enough work for a B200: vary timestamp / transaction subset / address
+ * (the freedom the node leaves, upow/manager.py:365-378,445-460, upow/node/main.py:580-600) and
+ * race the templates.  UPOW_EXHAUSTED when no template has a valid nonce below max_nonce. */
+int upow_search_any(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates, uint64_t max_nonce,
+                    uint32_t* out_index, upow_batch_item* out_item, upow_result* stats);
+
 /* The library carries several builds of the search kernel that differ only in how the integer
  * work is spread over the SM's alu and fma issue pipes (DESIGN.md "pipe balance"); results are
  * identical.  Variant 0 is the plain-CUDA kernel.  The default is the fastest one measured on

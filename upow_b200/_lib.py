@@ -19,7 +19,7 @@ EXPORTS = [
     "upow_set_template", "upow_search_min", "upow_sweep", "upow_search_batch", "upow_cancel",
     "upow_selftest", "upow_microbench_count", "upow_microbench", "upow_flush_l2", "upow_version",
     "upow_variant_count", "upow_variant_name", "upow_get_variant", "upow_set_variant",
-    "upow_sweep_noalloc", "upow_noalloc_last_error",
+    "upow_sweep_noalloc", "upow_noalloc_last_error", "upow_search_any",
 ]
 NOALLOC_MAX_HITS = 65536
 
@@ -101,6 +101,8 @@ def load():
     L.upow_sweep.argtypes = [vp, C.c_int, C.c_uint64, C.c_uint64, u32p, C.c_uint64, u64p, C.POINTER(Result)]
     L.upow_search_batch.argtypes = [vp, C.c_uint32, C.POINTER(Template), C.c_uint64, C.POINTER(BatchItem),
                                     C.POINTER(Result)]
+    L.upow_search_any.argtypes = [vp, C.c_uint32, C.POINTER(Template), C.c_uint64, C.POINTER(C.c_uint32),
+                                  C.POINTER(BatchItem), C.POINTER(Result)]
     L.upow_cancel.argtypes = [vp]
     L.upow_selftest.argtypes = [C.c_int]
     L.upow_microbench_count.argtypes = []
@@ -209,6 +211,27 @@ class Context:
         if rc < 0:
             raise UpowError(rc, "upow_search_batch", self._err())
         return [(bool(it.found), it.nonce, bytes(it.digest)) for it in items], stats
+
+    @staticmethod
+    def _template_array(templates):
+        arr = (Template * len(templates))()
+        for t, (prefix, prev_hash, n_int, cc) in zip(arr, templates):
+            C.memmove(t.prefix, bytes(prefix), len(prefix))
+            t.prefix_len = len(prefix)
+            C.memmove(t.prev_hash, bytes(prev_hash), 32)
+            t.n_int, t.charset_count = n_int, cc
+        return arr
+
+    def search_any(self, templates, max_nonce: int = 0):
+        """First success over many templates.  Returns (rc, index, nonce, digest, stats); rc 0 = found, 1 = none."""
+        templates = list(templates)
+        arr = self._template_array(templates)
+        idx, item, stats = C.c_uint32(0), BatchItem(), Result()
+        rc = self._L.upow_search_any(self._h, len(templates), arr, max_nonce, C.byref(idx), C.byref(item),
+                                     C.byref(stats))
+        if rc < 0:
+            raise UpowError(rc, "upow_search_any", self._err())
+        return rc, idx.value, item.nonce, bytes(item.digest), stats
 
     def cancel(self):
         self._L.upow_cancel(self._h)

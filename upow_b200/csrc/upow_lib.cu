@@ -718,9 +718,15 @@ int ensure_batch_capacity(upow_ctx* ctx, Device& d, uint32_t n) {
 
 // All templates assigned to one device: rounds over growing nonce chunks until every
 // template has its minimum or the space is exhausted.
+//
+// "any" mode (first_round != nullptr): every device walks the SAME fixed sequence of rounds
+// (fixed_h_round H values each) and stops once it has completed the earliest round in which any
+// device found something; the caller then picks the lowest template index among the finds of that
+// round, which makes the answer independent of the number of GPUs and of timing.
 int run_batch_on_device(upow_ctx* ctx, Device& d, const std::vector<BatchJob>& jobs, uint64_t max_nonce,
                         std::vector<unsigned long long>* best_out, std::vector<uint32_t>* digests_out,
-                        uint64_t* hashes, double* kernel_ms, uint32_t* launches) {
+                        uint64_t* hashes, double* kernel_ms, uint32_t* launches,
+                        std::atomic<uint32_t>* first_round = nullptr, uint64_t fixed_h_round = 0) {
     const uint32_t n = (uint32_t)jobs.size();
     best_out->assign(n, ~0ull);
     digests_out->assign((size_t)n * 8, 0);
@@ -739,8 +745,10 @@ int run_batch_on_device(upow_ctx* ctx, Device& d, const std::vector<BatchJob>& j
     uint32_t h_done = 0;
     bool has_v1 = false, has_v2 = false;
     for (auto& j : jobs) (j.tail.layout == LAYOUT_V1 ? has_v1 : has_v2) = true;
+    uint32_t round_no = 0;
     while (!active.empty() && h_done < h_total) {
         if (ctx->cancel.load(std::memory_order_relaxed)) return UPOW_CANCELLED;
+        if (first_round && round_no > first_round->load()) break;
         // round size: enough H values that the launch holds >= 16 items per warp, and at least
         // a quarter of the typical expected search length of the remaining templates
         double expect = 0;
@@ -753,6 +761,7 @@ int run_batch_on_device(upow_ctx* ctx, Device& d, const std::vector<BatchJob>& j
         uint64_t h_round = (uint64_t)(expect / 4 / 65536.0);
         const uint64_t h_min = ((uint64_t)16 * n_warps + 2047) / 2048 / active.size() + 1;
         h_round = std::max<uint64_t>(std::max<uint64_t>(h_round, h_min), 1);
+        if (first_round) h_round = fixed_h_round;
         h_round = std::min<uint64_t>(h_round, h_total - h_done);
         uint32_t hc = 64;
         while (hc > 1 && hc > h_round) hc >>= 1;
@@ -790,8 +799,13 @@ int run_batch_on_device(upow_ctx* ctx, Device& d, const std::vector<BatchJob>& j
         std::vector<uint32_t> still;
         for (uint32_t idx : active)
             if (best[idx] == ~0ull) still.push_back(idx);
+        if (first_round && still.size() != active.size()) {  // something was found in this round
+            uint32_t cur = first_round->load();
+            while (round_no < cur && !first_round->compare_exchange_weak(cur, round_no)) {}
+        }
         active.swap(still);
         h_done += (uint32_t)h_round;
+        round_no++;
     }
     batch_digest_kernel<<<(n + 127) / 128, 128, 0, d.stream>>>(d.d_jobs, d.d_best, n, d.d_bdigest);
     CU_TRY(ctx, cudaGetLastError());
@@ -801,6 +815,32 @@ int run_batch_on_device(upow_ctx* ctx, Device& d, const std::vector<BatchJob>& j
     return UPOW_OK;
 }
 
+}  // namespace
+
+// Shared front half of upow_search_batch / upow_search_any: validate and prepare every template.
+namespace {
+int prepare_templates(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates, std::vector<Prepared>* prep,
+                      const char* who) {
+    prep->resize(n_templates);
+    for (uint32_t i = 0; i < n_templates; i++) {
+        Slot s;
+        s.used = true;
+        if (templates[i].prefix_len != 134 && templates[i].prefix_len != 104) {
+            set_err(ctx, std::string(who) + ": template " + std::to_string(i) + ": prefix_len not 104/134");
+            return UPOW_E_ARG;
+        }
+        memcpy(s.prefix, templates[i].prefix, sizeof s.prefix);
+        s.prefix_len = (int)templates[i].prefix_len;
+        memcpy(s.prev_hash, templates[i].prev_hash, 32);
+        s.n_int = templates[i].n_int;
+        s.charset_count = templates[i].charset_count;
+        if (!prepare_slot(s, 0, &(*prep)[i])) {
+            set_err(ctx, std::string(who) + ": template " + std::to_string(i) + ": bad rule");
+            return UPOW_E_ARG;
+        }
+    }
+    return UPOW_OK;
+}
 }  // namespace
 
 extern "C" int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates,
@@ -814,24 +854,9 @@ extern "C" int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow
         const double t_begin = now_s();
         ctx->cancel.store(0, std::memory_order_relaxed);
         const int n_dev = (int)ctx->devs.size();
-        std::vector<Prepared> prep(n_templates);
-        for (uint32_t i = 0; i < n_templates; i++) {
-            Slot s;
-            s.used = true;
-            if (templates[i].prefix_len != 134 && templates[i].prefix_len != 104) {
-                set_err(ctx, "upow_search_batch: template " + std::to_string(i) + ": prefix_len not 104/134");
-                return UPOW_E_ARG;
-            }
-            memcpy(s.prefix, templates[i].prefix, sizeof s.prefix);
-            s.prefix_len = (int)templates[i].prefix_len;
-            memcpy(s.prev_hash, templates[i].prev_hash, 32);
-            s.n_int = templates[i].n_int;
-            s.charset_count = templates[i].charset_count;
-            if (!prepare_slot(s, 0, &prep[i])) {
-                set_err(ctx, "upow_search_batch: template " + std::to_string(i) + ": bad rule");
-                return UPOW_E_ARG;
-            }
-        }
+        std::vector<Prepared> prep;
+        int prc = prepare_templates(ctx, n_templates, templates, &prep, "upow_search_batch");
+        if (prc != UPOW_OK) return prc;
         // round-robin sharding of templates over the GPUs
         std::vector<std::vector<BatchJob>> jobs(n_dev);
         std::vector<std::vector<uint32_t>> owner(n_dev);
@@ -881,6 +906,101 @@ extern "C" int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow
             }
         }
         if (stats) stats->elapsed_s = now_s() - t_begin;
+        return UPOW_OK;
+    } catch (const std::exception& e) {
+        set_err(ctx, std::string("exception: ") + e.what());
+        return UPOW_E_INTERNAL;
+    } catch (...) {
+        set_err(ctx, "unknown exception");
+        return UPOW_E_INTERNAL;
+    }
+}
+
+
+extern "C" int upow_search_any(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates, uint64_t max_nonce,
+                               uint32_t* out_index, upow_batch_item* out_item, upow_result* stats) {
+    if (!ctx || !out_index || !out_item || (n_templates && !templates)) return UPOW_E_ARG;
+    try {
+        std::lock_guard<std::mutex> g(ctx->api_mu);
+        if (stats) memset(stats, 0, sizeof *stats);
+        memset(out_item, 0, sizeof *out_item);
+        *out_index = 0;
+        if (max_nonce == 0) max_nonce = NONCE_SPACE;
+        if (max_nonce > NONCE_SPACE) return UPOW_E_ARG;
+        if (n_templates == 0) return UPOW_EXHAUSTED;
+        const double t_begin = now_s();
+        ctx->cancel.store(0, std::memory_order_relaxed);
+        std::vector<Prepared> prep;
+        int prc = prepare_templates(ctx, n_templates, templates, &prep, "upow_search_any");
+        if (prc != UPOW_OK) return prc;
+        const int n_dev = (int)ctx->devs.size();
+        std::vector<std::vector<BatchJob>> jobs(n_dev);
+        std::vector<std::vector<uint32_t>> owner(n_dev);
+        double expect = 0;  // hashes until the FIRST success over all templates ~ the easiest rule's expectation
+        for (uint32_t i = 0; i < n_templates; i++) {
+            BatchJob j;
+            j.tail = prep[i].tail;
+            j.rule = prep[i].rule;
+            jobs[i % n_dev].push_back(j);
+            owner[i % n_dev].push_back(i);
+            double e = 1;
+            for (uint32_t q = 0; q < std::min<uint32_t>(j.rule.n_target, 16); q++) e *= 16;
+            e = e * 16.0 / j.rule.charset_count;
+            expect = (i == 0) ? e : std::min(expect, e);
+        }
+        // one round = every template advances by h_round H values; sized so that a round holds about a
+        // quarter of the expected work to the first success, and at least 16 items per warp per GPU
+        uint64_t h_round = (uint64_t)(expect / 4 / 65536.0 / n_templates);
+        const uint64_t per_dev = (n_templates + n_dev - 1) / n_dev;
+        const uint64_t h_min = ((uint64_t)16 * ctx->devs[0].batch_grid * 8 + 2047) / 2048 / per_dev + 1;
+        h_round = std::max<uint64_t>(std::max<uint64_t>(h_round, h_min), 1);
+        std::atomic<uint32_t> first_round{0xffffffffu};
+        std::vector<std::vector<unsigned long long>> best(n_dev);
+        std::vector<std::vector<uint32_t>> dig(n_dev);
+        std::vector<int> rcs(n_dev, UPOW_OK);
+        std::vector<uint64_t> hashes(n_dev, 0);
+        std::vector<double> ms(n_dev, 0.0);
+        std::vector<uint32_t> launches(n_dev, 0);
+        auto worker = [&](int di) {
+            rcs[di] = run_batch_on_device(ctx, ctx->devs[di], jobs[di], max_nonce, &best[di], &dig[di], &hashes[di],
+                                          &ms[di], &launches[di], &first_round, h_round);
+        };
+        if (n_dev == 1) worker(0);
+        else {
+            std::vector<std::thread> th;
+            for (int i = 0; i < n_dev; i++) th.emplace_back(worker, i);
+            for (auto& t : th) t.join();
+        }
+        for (int di = 0; di < n_dev; di++) {
+            if (rcs[di] != UPOW_OK) return rcs[di];
+            if (stats) {
+                stats->per_device_hashes[di] = hashes[di];
+                stats->per_device_kernel_ms[di] = ms[di];
+                stats->hashes_done += hashes[di];
+                stats->kernel_ms = std::max(stats->kernel_ms, ms[di]);
+                stats->launches += launches[di];
+            }
+        }
+        if (stats) stats->elapsed_s = now_s() - t_begin;
+        const uint32_t r = first_round.load();
+        if (r == 0xffffffffu) return UPOW_EXHAUSTED;
+        // finds of round r (and only those) are complete on every device: nonce < (r+1) * h_round * 2^16
+        const unsigned long long limit = std::min<unsigned long long>((unsigned long long)(r + 1) * h_round << 16, max_nonce);
+        uint32_t win = 0xffffffffu;
+        int win_dev = -1;
+        size_t win_k = 0;
+        for (int di = 0; di < n_dev; di++)
+            for (size_t k = 0; k < owner[di].size(); k++)
+                if (best[di][k] < limit && owner[di][k] < win) { win = owner[di][k]; win_dev = di; win_k = k; }
+        if (win_dev < 0) { set_err(ctx, "upow_search_any: inconsistent round bookkeeping"); return UPOW_E_INTERNAL; }
+        out_item->found = 1;
+        out_item->nonce = (uint32_t)best[win_dev][win_k];
+        for (int w = 0; w < 8; w++) store_be32(out_item->digest + 4 * w, dig[win_dev][win_k * 8 + w]);
+        if (!host_verify(prep[win], out_item->nonce, out_item->digest)) {
+            set_err(ctx, "upow_search_any: result failed the host cross-check");
+            return UPOW_E_INTERNAL;
+        }
+        *out_index = win;
         return UPOW_OK;
     } catch (const std::exception& e) {
         set_err(ctx, std::string("exception: ") + e.what());
