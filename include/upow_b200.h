@@ -100,6 +100,16 @@ typedef struct upow_batch_item {
     uint8_t digest[32];
 } upow_batch_item;
 
+/* One finished block for upow_verify_blocks (192 bytes). */
+typedef struct upow_block {
+    uint8_t content[140];    /* bytes.fromhex(block_content): 138 or 108 used (upow/manager.py:401-419) */
+    uint32_t content_len;
+    uint8_t prev_hash[32];   /* bytes.fromhex(last_block["hash"]) the block must chain to */
+    int32_t n_int;           /* floor(difficulty) */
+    int32_t charset_count;   /* ceil(16*(1-difficulty%1)), 16 when the fraction is 0 */
+    uint32_t reserved[2];
+} upow_block;
+
 /* Creates a context driving n_devices GPUs (device_ids == NULL: devices 0..n-1; n_devices == 0:
  * every visible device, at most UPOW_MAX_DEVICES).  Replaces the worker-pool set-up of
  * miner.py:139-148 (one OS process per worker) by one host thread per GPU. */
@@ -148,6 +158,13 @@ int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow_template* 
  * race the templates.  UPOW_EXHAUSTED when no template has a valid nonce below max_nonce. */
 int upow_search_any(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates, uint64_t max_nonce,
                     uint32_t* out_index, upow_batch_item* out_item, upow_result* stats);
+
+/* Batch form of the node's check_block_is_valid (upow/manager.py:130-151): sha256(content) and the
+ * difficulty rule against prev_hash, for n blocks at once (chain sync verifies them one by one,
+ * upow/node/main.py:97-150).  out_valid[i] = 1 valid, 0 not valid, 0xff content_len is neither 138
+ * nor 108; out_digests (may be NULL) receives 32 bytes per block.  Blocks are split over the GPUs. */
+int upow_verify_blocks(upow_ctx* ctx, uint32_t n_blocks, const upow_block* blocks, uint8_t* out_valid,
+                       uint8_t* out_digests, upow_result* stats);
 
 /* The library carries several builds of the search kernel that differ only in how the integer
  * work is spread over the SM's alu and fma issue pipes (DESIGN.md "pipe balance"); results are

@@ -83,6 +83,10 @@ uint32_t hh_tuned_a64(const Tail* t, uint32_t nonce) {
 int hh_prefilter(const Rule* r, uint32_t a64) { return a64 + r->sub0 < r->range0; }
 int hh_rule_accepts(const Rule* r, const uint32_t d[8]) { return rule_accepts(*r, d); }
 
+int hh_digest_accepts_prev(const uint32_t prev[8], int n_int, int cc, const uint32_t d[8]) {
+    return digest_accepts_prev(prev, n_int, cc, d);
+}
+
 void hh_set_timestamp(uint8_t* prefix, int len, uint32_t ts) { set_prefix_timestamp(prefix, len, ts); }
 uint32_t hh_get_timestamp(const uint8_t* prefix, int len) { return get_prefix_timestamp(prefix, len); }
 }

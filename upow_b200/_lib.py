@@ -19,7 +19,7 @@ EXPORTS = [
     "upow_set_template", "upow_search_min", "upow_sweep", "upow_search_batch", "upow_cancel",
     "upow_selftest", "upow_microbench_count", "upow_microbench", "upow_flush_l2", "upow_version",
     "upow_variant_count", "upow_variant_name", "upow_get_variant", "upow_set_variant",
-    "upow_sweep_noalloc", "upow_noalloc_last_error", "upow_search_any",
+    "upow_sweep_noalloc", "upow_noalloc_last_error", "upow_search_any", "upow_verify_blocks",
 ]
 NOALLOC_MAX_HITS = 65536
 
@@ -65,6 +65,11 @@ class Template(C.Structure):
                 ("n_int", C.c_int32), ("charset_count", C.c_int32)]
 
 
+class Block(C.Structure):
+    _fields_ = [("content", C.c_uint8 * 140), ("content_len", C.c_uint32), ("prev_hash", C.c_uint8 * 32),
+                ("n_int", C.c_int32), ("charset_count", C.c_int32), ("reserved", C.c_uint32 * 2)]
+
+
 class BatchItem(C.Structure):
     _fields_ = [("found", C.c_int32), ("nonce", C.c_uint32), ("digest", C.c_uint8 * 32)]
 
@@ -103,6 +108,7 @@ def load():
                                     C.POINTER(Result)]
     L.upow_search_any.argtypes = [vp, C.c_uint32, C.POINTER(Template), C.c_uint64, C.POINTER(C.c_uint32),
                                   C.POINTER(BatchItem), C.POINTER(Result)]
+    L.upow_verify_blocks.argtypes = [vp, C.c_uint32, C.POINTER(Block), C.c_char_p, C.c_char_p, C.POINTER(Result)]
     L.upow_cancel.argtypes = [vp]
     L.upow_selftest.argtypes = [C.c_int]
     L.upow_microbench_count.argtypes = []
@@ -232,6 +238,27 @@ class Context:
         if rc < 0:
             raise UpowError(rc, "upow_search_any", self._err())
         return rc, idx.value, item.nonce, bytes(item.digest), stats
+
+    def verify_blocks(self, blocks, want_digests: bool = True):
+        """blocks: iterable of (content bytes, prev_hash bytes, n_int, charset_count).
+        Returns (verdicts list of 1/0/255, digests list of bytes or None, stats)."""
+        blocks = list(blocks)
+        arr = (Block * max(len(blocks), 1))()
+        for rec, (content, prev_hash, n_int, cc) in zip(arr, blocks):
+            content = bytes(content)
+            C.memmove(rec.content, content[:140], min(len(content), 140))
+            rec.content_len = len(content)
+            C.memmove(rec.prev_hash, bytes(prev_hash), 32)
+            rec.n_int, rec.charset_count = n_int, cc
+        valid = C.create_string_buffer(max(len(blocks), 1))
+        dig = C.create_string_buffer(32 * max(len(blocks), 1)) if want_digests else None
+        stats = Result()
+        rc = self._L.upow_verify_blocks(self._h, len(blocks), arr, valid, dig, C.byref(stats))
+        if rc != UPOW_OK:
+            raise UpowError(rc, "upow_verify_blocks", self._err())
+        verdicts = list(valid.raw[: len(blocks)])
+        digests = [dig.raw[32 * i: 32 * i + 32] for i in range(len(blocks))] if want_digests else None
+        return verdicts, digests, stats
 
     def cancel(self):
         self._L.upow_cancel(self._h)

@@ -425,6 +425,73 @@ __global__ void __launch_bounds__(256, 3) batch_kernel(const __grid_constant__ B
     if (lane == 0 && done) atomicAdd(&A.res->items_done, (unsigned long long)done);
 }
 
+// ---------------------------------------------------------------------------------------
+// Batch block verifier: check_block_is_valid (upow/manager.py:130-151) for many
+// finished blocks at once -- what chain sync does one block at a time (upow/node/main.py:97-150).
+// One thread hashes one block (2 or 3 compressions).  The records (192 B each, = upow_block) are
+// staged through shared memory with coalesced 16-byte loads; this kernel is HBM-bound:
+// 192 B in + 33 B out per block.
+struct VerifyRecord {          // must match upow_block in include/upow_b200.h
+    uint8_t content[140];
+    uint32_t content_len;
+    uint8_t prev_hash[32];
+    int32_t n_int;
+    int32_t charset_count;
+    uint32_t pad[2];
+};
+static_assert(sizeof(VerifyRecord) == 192, "VerifyRecord must be 192 bytes");
+
+constexpr int VERIFY_THREADS = 128;
+
+__global__ void __launch_bounds__(VERIFY_THREADS) verify_kernel(const VerifyRecord* recs, uint32_t n, uint8_t* out_valid,
+                                                               uint32_t* out_digests) {
+    __shared__ uint4 stage[VERIFY_THREADS * 12];   // 128 records x 192 B
+    const uint32_t base = blockIdx.x * VERIFY_THREADS;
+    const uint32_t n_here = min((uint32_t)VERIFY_THREADS, n - base);
+    const uint4* src = reinterpret_cast<const uint4*>(recs + base);
+    for (uint32_t i = threadIdx.x; i < n_here * 12; i += VERIFY_THREADS) stage[i] = src[i];
+    __syncthreads();
+    if (threadIdx.x >= n_here) return;
+    const uint32_t* rec = reinterpret_cast<const uint32_t*>(stage) + threadIdx.x * 48;
+    const uint32_t len = rec[35];
+    uint8_t verdict = 0;
+    uint32_t st[8] = {0x6a09e667, 0xbb67ae85, 0x3c6ef372, 0xa54ff53a, 0x510e527f, 0x9b05688c, 0x1f83d9ab, 0x5be0cd19};
+    if (len == 138 || len == 108) {   // the only two lengths the node accepts (upow/manager.py:401-419)
+        const uint32_t n_blocks = (len + 9 + 63) / 64;
+        for (uint32_t b = 0; b < n_blocks; b++) {
+            uint32_t w[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) {
+                const uint32_t off = 64 * b + 4 * i;           // byte offset of this word in the padded message
+                uint32_t v = 0;
+                if (off + 4 <= len) v = bswap32(rec[off >> 2]);
+                else if (off <= len) {                          // word holding the tail of the content and the 0x80
+                    const uint32_t keep = len - off;            // 0..3 content bytes
+                    const uint32_t raw = off < 140 ? bswap32(rec[off >> 2]) : 0u;
+                    v = keep ? (raw & (0xffffffffu << (32 - 8 * keep))) : 0u;
+                    v |= 0x80u << (24 - 8 * keep);
+                }
+                if (b == n_blocks - 1 && i == 15) v = len * 8;
+                w[i] = v;
+            }
+            compress_rolled(st, w, K_DEV);
+        }
+        uint32_t prev[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) prev[i] = bswap32(rec[36 + i]);
+        verdict = digest_accepts_prev(prev, (int)rec[44], (int)rec[45], st) ? 1 : 0;
+    } else {
+        verdict = 0xff;   // malformed length: the reference's split_block_content asserts
+#pragma unroll
+        for (int i = 0; i < 8; i++) st[i] = 0;
+    }
+    out_valid[base + threadIdx.x] = verdict;
+    if (out_digests) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) out_digests[(size_t)(base + threadIdx.x) * 8 + i] = st[i];
+    }
+}
+
 // Digests of the batch winners: thread i handles job i (skipped when nothing was found).
 __global__ void batch_digest_kernel(const BatchJob* jobs, const unsigned long long* best, uint32_t n_jobs,
                                     uint32_t* out) {

@@ -186,6 +186,23 @@ inline bool prepare_rule(const uint8_t prev_hash[32], int n_int, int charset_cou
     return true;
 }
 
+// The node-side rule, upow/manager.py:130-151, straight from the previous block's hash (as digest-style
+// big-endian words) without a prepared Rule: block_hash.startswith(last_hash[-N:]) and, with a fractional
+// difficulty, block_hash[N] in charset[:count].  N == 0 and N > 64 select the whole hash (Python slices);
+// N >= 64 with a charset limit would raise IndexError in the reference and is reported as not valid.
+UPOW_HD uint32_t nibble_of(const uint32_t w[8], int i) { return (w[i >> 3] >> (28 - 4 * (i & 7))) & 0xf; }
+UPOW_HD bool digest_accepts_prev(const uint32_t prev[8], int n_int, int charset_count, const uint32_t d[8]) {
+    if (n_int < 0 || charset_count < 1 || charset_count > 16) return false;
+    const int n_target = (n_int == 0 || n_int > 64) ? 64 : n_int;
+    for (int i = 0; i < n_target; i++)
+        if (nibble_of(d, i) != nibble_of(prev, 64 - n_target + i)) return false;
+    if (charset_count < 16) {
+        if (n_int > 63) return false;
+        if (nibble_of(d, n_int) >= (uint32_t)charset_count) return false;
+    }
+    return true;
+}
+
 // Generic check of a full digest against the rule (device slow path + host cross-check).
 UPOW_HD bool rule_accepts(const Rule& r, const uint32_t d[8]) {
     const uint32_t full = r.n_target >> 3, part = r.n_target & 7;

@@ -65,6 +65,11 @@ struct Device {
     unsigned long long* d_best = nullptr;
     uint32_t* d_bdigest = nullptr;
     uint32_t batch_cap = 0;
+    // block verifier
+    VerifyRecord* d_vrecs = nullptr;
+    uint8_t* d_vvalid = nullptr;
+    uint32_t* d_vdig = nullptr;
+    uint32_t verify_cap = 0;
 };
 
 }  // namespace
@@ -135,6 +140,7 @@ void destroy_device(Device& d) {
     if (d.ev1) cudaEventDestroy(d.ev1);
     cudaFree(d.d_res); cudaFree(d.d_out); cudaFree(d.d_digest); cudaFree(d.d_flush);
     cudaFree(d.d_jobs); cudaFree(d.d_active); cudaFree(d.d_best); cudaFree(d.d_bdigest);
+    cudaFree(d.d_vrecs); cudaFree(d.d_vvalid); cudaFree(d.d_vdig);
     if (d.h_res) cudaFreeHost(d.h_res);
     if (d.h_digest) cudaFreeHost(d.h_digest);
     if (d.h_one) cudaFreeHost(d.h_one);
@@ -1001,6 +1007,88 @@ extern "C" int upow_search_any(upow_ctx* ctx, uint32_t n_templates, const upow_t
             return UPOW_E_INTERNAL;
         }
         *out_index = win;
+        return UPOW_OK;
+    } catch (const std::exception& e) {
+        set_err(ctx, std::string("exception: ") + e.what());
+        return UPOW_E_INTERNAL;
+    } catch (...) {
+        set_err(ctx, "unknown exception");
+        return UPOW_E_INTERNAL;
+    }
+}
+
+
+namespace {
+static_assert(sizeof(upow_block) == sizeof(VerifyRecord), "upow_block and VerifyRecord must have one layout");
+
+int verify_on_device(upow_ctx* ctx, Device& d, const upow_block* blocks, uint32_t n, uint8_t* out_valid,
+                     uint8_t* out_digests, double* kernel_ms) {
+    if (n == 0) return UPOW_OK;
+    CU_TRY(ctx, cudaSetDevice(d.id));
+    if (n > d.verify_cap) {
+        cudaFree(d.d_vrecs); cudaFree(d.d_vvalid); cudaFree(d.d_vdig);
+        d.d_vrecs = nullptr; d.d_vvalid = nullptr; d.d_vdig = nullptr; d.verify_cap = 0;
+        CU_TRY(ctx, cudaMalloc(&d.d_vrecs, sizeof(VerifyRecord) * (size_t)n));
+        CU_TRY(ctx, cudaMalloc(&d.d_vvalid, n));
+        CU_TRY(ctx, cudaMalloc(&d.d_vdig, 32 * (size_t)n));
+        d.verify_cap = n;
+    }
+    CU_TRY(ctx, cudaMemcpyAsync(d.d_vrecs, blocks, sizeof(VerifyRecord) * (size_t)n, cudaMemcpyHostToDevice, d.stream));
+    CU_TRY(ctx, cudaEventRecord(d.ev0, d.stream));
+    verify_kernel<<<(n + VERIFY_THREADS - 1) / VERIFY_THREADS, VERIFY_THREADS, 0, d.stream>>>(
+        d.d_vrecs, n, d.d_vvalid, out_digests ? d.d_vdig : nullptr);
+    CU_TRY(ctx, cudaGetLastError());
+    CU_TRY(ctx, cudaEventRecord(d.ev1, d.stream));
+    CU_TRY(ctx, cudaMemcpyAsync(out_valid, d.d_vvalid, n, cudaMemcpyDeviceToHost, d.stream));
+    std::vector<uint32_t> words;
+    if (out_digests) {
+        words.resize((size_t)n * 8);
+        CU_TRY(ctx, cudaMemcpyAsync(words.data(), d.d_vdig, 32 * (size_t)n, cudaMemcpyDeviceToHost, d.stream));
+    }
+    CU_TRY(ctx, cudaStreamSynchronize(d.stream));
+    if (out_digests)
+        for (size_t i = 0; i < words.size(); i++) store_be32(out_digests + 4 * i, words[i]);
+    float ms = 0;
+    CU_TRY(ctx, cudaEventElapsedTime(&ms, d.ev0, d.ev1));
+    *kernel_ms = ms;
+    return UPOW_OK;
+}
+}  // namespace
+
+extern "C" int upow_verify_blocks(upow_ctx* ctx, uint32_t n_blocks, const upow_block* blocks, uint8_t* out_valid,
+                                  uint8_t* out_digests, upow_result* stats) {
+    if (!ctx || (n_blocks && (!blocks || !out_valid))) return UPOW_E_ARG;
+    try {
+        std::lock_guard<std::mutex> g(ctx->api_mu);
+        if (stats) memset(stats, 0, sizeof *stats);
+        const double t_begin = now_s();
+        const int n_dev = (int)ctx->devs.size();
+        std::vector<int> rcs(n_dev, UPOW_OK);
+        std::vector<double> ms(n_dev, 0.0);
+        std::vector<uint32_t> cut(n_dev + 1);
+        for (int i = 0; i <= n_dev; i++) cut[i] = (uint32_t)((uint64_t)n_blocks * i / n_dev);
+        auto worker = [&](int di) {
+            const uint32_t lo = cut[di], cnt = cut[di + 1] - cut[di];
+            rcs[di] = verify_on_device(ctx, ctx->devs[di], blocks + lo, cnt, out_valid + lo,
+                                       out_digests ? out_digests + 32 * (size_t)lo : nullptr, &ms[di]);
+        };
+        if (n_dev == 1) worker(0);
+        else {
+            std::vector<std::thread> th;
+            for (int i = 0; i < n_dev; i++) th.emplace_back(worker, i);
+            for (auto& t : th) t.join();
+        }
+        for (int di = 0; di < n_dev; di++) {
+            if (rcs[di] != UPOW_OK) return rcs[di];
+            if (stats) {
+                stats->per_device_hashes[di] = cut[di + 1] - cut[di];
+                stats->per_device_kernel_ms[di] = ms[di];
+                stats->hashes_done += cut[di + 1] - cut[di];
+                stats->kernel_ms = std::max(stats->kernel_ms, ms[di]);
+                if (cut[di + 1] > cut[di]) stats->launches++;
+            }
+        }
+        if (stats) stats->elapsed_s = now_s() - t_begin;
         return UPOW_OK;
     } catch (const std::exception& e) {
         set_err(ctx, std::string("exception: ") + e.what());
