@@ -166,6 +166,13 @@ int upow_search_any(upow_ctx* ctx, uint32_t n_templates, const upow_template* te
 int upow_verify_blocks(upow_ctx* ctx, uint32_t n_blocks, const upow_block* blocks, uint8_t* out_valid,
                        uint8_t* out_digests, upow_result* stats);
 
+/* SHA-256 of n variable-length messages: message i is data[offsets[i] .. offsets[i+1]) (offsets has
+ * n+1 entries, non-decreasing); out receives 32 bytes per message.  This is the per-transaction hashing
+ * of upow/node/main.py:692 and upow/manager.py:365-378 (merkle tree) and Transaction.hash
+ * (upow/upow_transactions/transaction.py:85-88) in one call.  Messages are split over the GPUs. */
+int upow_sha256_batch(upow_ctx* ctx, uint32_t n, const uint8_t* data, const uint64_t* offsets, uint8_t* out,
+                      upow_result* stats);
+
 /* The library carries several builds of the search kernel that differ only in how the integer
  * work is spread over the SM's alu and fma issue pipes (DESIGN.md "pipe balance"); results are
  * identical.  Variant 0 is the plain-CUDA kernel.  The default is the fastest one measured on

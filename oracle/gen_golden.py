@@ -10,6 +10,7 @@ Run in the build container (needs /root/reference):
   replaced, plus the verdict of ``upow.manager.check_block_is_valid``
   (upow/manager.py:130-151) on the resulting block, also run verbatim.
 * ``verifier_vectors.json``: check_block_is_valid verdicts on near-miss blocks.
+* ``merkle_tree_vectors.json``: get_transactions_merkle_tree (upow/manager.py:365-378) on random blobs.
 * ``sweep_t0v1_d5.u32`` (+ ``.json``): all valid nonces of the full 2^32 sweep of
   template T0-v1 at difficulty 5.0, enumerated by the C
   oracle (oracle/upow_oracle.c, full-message SHA-256 per nonce); the script refuses
@@ -99,6 +100,17 @@ def verifier_vectors(vecs):
     return out
 
 
+def merkle_vectors():
+    """get_transactions_merkle_tree (upow/manager.py:365-378) run verbatim on random transaction blobs."""
+    mgr = ref_loader.load_manager()
+    rng = random.Random(3)
+    cases = []
+    for n in (0, 1, 2, 7, 40):
+        txs = [rng.randbytes(rng.randrange(120, 400)).hex() for _ in range(n)]
+        cases.append({"txs": txs, "merkle_tree": mgr.get_transactions_merkle_tree(txs)})
+    return cases
+
+
 def sweep_fixture():
     prefix = O.t0_prefix(5.0)
     rule = O.Rule(5.0, O.T0_PREV_HASH)
@@ -136,6 +148,8 @@ def main():
     with open(os.path.join(GOLDEN, "verifier_vectors.json"), "w") as f:
         json.dump(ver, f, indent=1)
     print(f"{len(ver)} verifier vectors ({sum(v['valid'] for v in ver)} valid)")
+    with open(os.path.join(GOLDEN, "merkle_tree_vectors.json"), "w") as f:
+        json.dump(merkle_vectors(), f)
     if args.sweep:
         sweep_fixture()
 

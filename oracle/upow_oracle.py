@@ -78,6 +78,12 @@ def calculate_merkle_root(transactions) -> str:
     return hashlib.sha256(b"".join(bytes.fromhex(tx) for tx in transactions)).hexdigest()
 
 
+def transactions_merkle_tree(txs_hex) -> str:
+    """upow/manager.py:365-378: sort the transactions' bytes, sha256 each, sha256 the concatenation."""
+    ordered = sorted(bytes.fromhex(t) for t in txs_hex)
+    return hashlib.sha256(b"".join(hashlib.sha256(b).digest() for b in ordered)).hexdigest()
+
+
 # --------------------------------------------------------------------------
 # rule + prefix (miner.py:34-49, 74-82)
 # --------------------------------------------------------------------------

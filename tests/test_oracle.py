@@ -172,3 +172,12 @@ def test_reference_verbatim_matches_oracle():
         n = O.min_valid_nonce(prefix, O.Rule(d, prev))
         assert out["block_content"] == (prefix + n.to_bytes(4, "little")).hex()
         assert ref_loader.check_block_is_valid(out["block_content"], d, {"hash": prev, "id": 7})
+
+
+def test_merkle_tree_restatement_against_reference_vectors():
+    import json, os
+    from conftest import GOLDEN
+    cases = json.load(open(os.path.join(GOLDEN, "merkle_tree_vectors.json")))
+    assert len(cases) == 5
+    for c in cases:
+        assert O.transactions_merkle_tree(c["txs"]) == c["merkle_tree"]

@@ -19,7 +19,7 @@ EXPORTS = [
     "upow_set_template", "upow_search_min", "upow_sweep", "upow_search_batch", "upow_cancel",
     "upow_selftest", "upow_microbench_count", "upow_microbench", "upow_flush_l2", "upow_version",
     "upow_variant_count", "upow_variant_name", "upow_get_variant", "upow_set_variant",
-    "upow_sweep_noalloc", "upow_noalloc_last_error", "upow_search_any", "upow_verify_blocks",
+    "upow_sweep_noalloc", "upow_noalloc_last_error", "upow_search_any", "upow_verify_blocks", "upow_sha256_batch",
 ]
 NOALLOC_MAX_HITS = 65536
 
@@ -109,6 +109,7 @@ def load():
     L.upow_search_any.argtypes = [vp, C.c_uint32, C.POINTER(Template), C.c_uint64, C.POINTER(C.c_uint32),
                                   C.POINTER(BatchItem), C.POINTER(Result)]
     L.upow_verify_blocks.argtypes = [vp, C.c_uint32, C.POINTER(Block), C.c_char_p, C.c_char_p, C.POINTER(Result)]
+    L.upow_sha256_batch.argtypes = [vp, C.c_uint32, C.c_char_p, u64p, C.c_char_p, C.POINTER(Result)]
     L.upow_cancel.argtypes = [vp]
     L.upow_selftest.argtypes = [C.c_int]
     L.upow_microbench_count.argtypes = []
@@ -259,6 +260,23 @@ class Context:
         verdicts = list(valid.raw[: len(blocks)])
         digests = [dig.raw[32 * i: 32 * i + 32] for i in range(len(blocks))] if want_digests else None
         return verdicts, digests, stats
+
+    def sha256_many(self, messages):
+        """SHA-256 of every message (bytes) in one device call.  Returns (list of 32-byte digests, stats)."""
+        messages = [bytes(m) for m in messages]
+        n = len(messages)
+        offs = (C.c_uint64 * (n + 1))()
+        total = 0
+        for i, m in enumerate(messages):
+            offs[i] = total
+            total += len(m)
+        offs[n] = total
+        out = C.create_string_buffer(32 * max(n, 1))
+        stats = Result()
+        rc = self._L.upow_sha256_batch(self._h, n, b"".join(messages), offs, out, C.byref(stats))
+        if rc != UPOW_OK:
+            raise UpowError(rc, "upow_sha256_batch", self._err())
+        return [out.raw[32 * i: 32 * i + 32] for i in range(n)], stats
 
     def cancel(self):
         self._L.upow_cancel(self._h)

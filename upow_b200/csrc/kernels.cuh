@@ -492,6 +492,69 @@ __global__ void __launch_bounds__(VERIFY_THREADS) verify_kernel(const VerifyReco
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// Generic batched SHA-256 of variable-length messages: the per-transaction hashes
+// of upow/node/main.py:692 / upow/manager.py:365-378 / Transaction.hash.  One thread per message,
+// fully unrolled compression; messages sit back to back in one byte buffer (any alignment) and are read
+// with aligned 32-bit loads re-aligned and byte-swapped by one PRMT per word.  The buffer must be
+// readable 8 bytes past its end (the library pads its device copy).  Bound by the alu pipe like the
+// search kernels (about 1300 instructions per 64 bytes), not by HBM.
+__device__ __forceinline__ void compress_unrolled(uint32_t st[8], uint32_t (&w)[16]) {
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+#pragma unroll
+    for (int t = 0; t < 64; t++) {
+        if (t >= 16)
+            w[t & 15] = w[t & 15] + small_sigma0(w[(t + 1) & 15]) + w[(t + 9) & 15] + small_sigma1(w[(t + 14) & 15]);
+        uint32_t t1 = h + big_sigma1(e) + ch(e, f, g) + (Kc(t) + w[t & 15]);
+        uint32_t t2 = big_sigma0(a) + maj(a, b, c);
+        h = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
+    }
+    st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
+}
+
+__global__ void __launch_bounds__(128) sha256_batch_kernel(const uint8_t* data, const unsigned long long* offsets,
+                                                          uint32_t n, uint32_t* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned long long beg = offsets[i];
+    const unsigned long long len = offsets[i + 1] - beg;
+    const uint32_t* words = reinterpret_cast<const uint32_t*>(data) + (beg >> 2);   // aligned word holding byte `beg`
+    const uint32_t mis = (uint32_t)(beg & 3);
+    // big-endian word from two consecutive little-endian aligned words lo, hi at byte misalignment `mis`
+    const uint32_t sel = mis == 0 ? 0x0123u : mis == 1 ? 0x1234u : mis == 2 ? 0x2345u : 0x3456u;
+    uint32_t st[8] = {0x6a09e667, 0xbb67ae85, 0x3c6ef372, 0xa54ff53a, 0x510e527f, 0x9b05688c, 0x1f83d9ab, 0x5be0cd19};
+    const unsigned long long n_blocks = (len + 9 + 63) / 64;
+    for (unsigned long long b = 0; b < n_blocks; b++) {
+        uint32_t w[16];
+        const unsigned long long base = 64 * b;
+        uint32_t lo = (base < len) ? __ldg(words + base / 4) : 0u;
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+            const unsigned long long pos = base + 4 * j;
+            uint32_t v = 0;
+            if (pos < len) {
+                const uint32_t hi = __ldg(words + pos / 4 + 1);     // may lie past the message: masked below / padded buffer
+                v = __byte_perm(lo, hi, sel);
+                lo = hi;
+                if (pos + 4 > len) {                                 // last, partial word: keep len-pos bytes, then 0x80
+                    const uint32_t keep = (uint32_t)(len - pos);    // 1..3
+                    v = (v & (0xffffffffu << (32 - 8 * keep))) | (0x80u << (24 - 8 * keep));
+                }
+            } else if (pos == len) {
+                v = 0x80000000u;
+            }
+            w[j] = v;
+        }
+        if (b == n_blocks - 1) {
+            w[14] = (uint32_t)((len * 8) >> 32);
+            w[15] = (uint32_t)(len * 8);
+        }
+        compress_unrolled(st, w);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) out[(size_t)i * 8 + k] = st[k];
+}
+
 // Digests of the batch winners: thread i handles job i (skipped when nothing was found).
 __global__ void batch_digest_kernel(const BatchJob* jobs, const unsigned long long* best, uint32_t n_jobs,
                                     uint32_t* out) {

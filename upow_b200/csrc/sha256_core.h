@@ -74,16 +74,6 @@ UPOW_HD uint32_t bswap32(uint32_t x) {
 #endif
 }
 
-// One round on named registers: updates d (becomes the new e) and h (becomes the new a).
-// The caller rotates the names, so no register moves are generated.
-#define UPOW_ROUND(a, b, c, d, e, f, g, h, kw)                                          \
-    do {                                                                                \
-        uint32_t t1_ = (h) + ::upow::big_sigma1(e) + ::upow::ch(e, f, g) + (kw);        \
-        uint32_t t2_ = ::upow::big_sigma0(a) + ::upow::maj(a, b, c);                    \
-        (d) += t1_;                                                                     \
-        (h) = t1_ + t2_;                                                                \
-    } while (0)
-
 // Rolled, fully general compression.  Used by the host-side midstate computation, by the
 // device slow path (re-check of a pre-filter hit, full digest of the winner) and by the
 // selftest kernel.  `k` is a pointer so device code can hand in its __constant__ copy.

@@ -45,7 +45,7 @@ struct Slot {
 struct Device {
     int id = -1;
     int sm_count = 0;
-    int grid_blocks = 0;
+    int grid_blocks = 0;   // persistent grid of the strided kernel
     int variant_grid[16] = {0};
     int batch_grid = 0;
     cudaDeviceProp prop;
@@ -125,7 +125,7 @@ int init_device(upow_ctx* ctx, Device& d, int id) {
     CU_TRY(ctx, cudaMallocHost(&d.h_one, sizeof(unsigned int)));
     *d.h_one = 1;
     int per_sm = 0;
-    CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, search_kernel<LAYOUT_V1, MODE_MIN, 1>, 256, 0));
+    CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, search_strided_kernel<LAYOUT_V1, MODE_MIN>, 256, 0));
     if (per_sm < 1) per_sm = 1;
     d.grid_blocks = d.sm_count * per_sm;
     return UPOW_OK;
@@ -1071,6 +1071,94 @@ extern "C" int upow_verify_blocks(upow_ctx* ctx, uint32_t n_blocks, const upow_b
             const uint32_t lo = cut[di], cnt = cut[di + 1] - cut[di];
             rcs[di] = verify_on_device(ctx, ctx->devs[di], blocks + lo, cnt, out_valid + lo,
                                        out_digests ? out_digests + 32 * (size_t)lo : nullptr, &ms[di]);
+        };
+        if (n_dev == 1) worker(0);
+        else {
+            std::vector<std::thread> th;
+            for (int i = 0; i < n_dev; i++) th.emplace_back(worker, i);
+            for (auto& t : th) t.join();
+        }
+        for (int di = 0; di < n_dev; di++) {
+            if (rcs[di] != UPOW_OK) return rcs[di];
+            if (stats) {
+                stats->per_device_hashes[di] = cut[di + 1] - cut[di];
+                stats->per_device_kernel_ms[di] = ms[di];
+                stats->hashes_done += cut[di + 1] - cut[di];
+                stats->kernel_ms = std::max(stats->kernel_ms, ms[di]);
+                if (cut[di + 1] > cut[di]) stats->launches++;
+            }
+        }
+        if (stats) stats->elapsed_s = now_s() - t_begin;
+        return UPOW_OK;
+    } catch (const std::exception& e) {
+        set_err(ctx, std::string("exception: ") + e.what());
+        return UPOW_E_INTERNAL;
+    } catch (...) {
+        set_err(ctx, "unknown exception");
+        return UPOW_E_INTERNAL;
+    }
+}
+
+
+namespace {
+// messages [m_lo, m_hi) on one device; device buffers are per call (sizes vary widely)
+int sha_batch_on_device(upow_ctx* ctx, Device& d, const uint8_t* data, const uint64_t* offsets, uint32_t m_lo,
+                        uint32_t m_hi, uint8_t* out, double* kernel_ms) {
+    const uint32_t n = m_hi - m_lo;
+    if (n == 0) return UPOW_OK;
+    CU_TRY(ctx, cudaSetDevice(d.id));
+    const uint64_t b_lo = offsets[m_lo], b_hi = offsets[m_hi];
+    const uint64_t bytes = b_hi - b_lo;
+    uint8_t* d_data = nullptr;
+    unsigned long long* d_off = nullptr;
+    uint32_t* d_out = nullptr;
+    int rc = UPOW_E_CUDA;
+    std::vector<unsigned long long> rel(n + 1);
+    for (uint32_t i = 0; i <= n; i++) rel[i] = offsets[m_lo + i] - b_lo;
+    std::vector<uint32_t> words((size_t)n * 8);
+    do {
+        cudaError_t e;
+        if ((e = cudaMalloc(&d_data, bytes + 16)) != cudaSuccess) { set_err(ctx, cudaGetErrorString(e)); break; }
+        if ((e = cudaMalloc(&d_off, sizeof(unsigned long long) * (n + 1))) != cudaSuccess) { set_err(ctx, cudaGetErrorString(e)); break; }
+        if ((e = cudaMalloc(&d_out, 32 * (size_t)n)) != cudaSuccess) { set_err(ctx, cudaGetErrorString(e)); break; }
+        if (bytes) cudaMemcpyAsync(d_data, data + b_lo, bytes, cudaMemcpyHostToDevice, d.stream);
+        cudaMemsetAsync(d_data + bytes, 0, 16, d.stream);
+        cudaMemcpyAsync(d_off, rel.data(), sizeof(unsigned long long) * (n + 1), cudaMemcpyHostToDevice, d.stream);
+        cudaEventRecord(d.ev0, d.stream);
+        sha256_batch_kernel<<<(n + 127) / 128, 128, 0, d.stream>>>(d_data, d_off, n, d_out);
+        if ((e = cudaGetLastError()) != cudaSuccess) { set_err(ctx, cudaGetErrorString(e)); break; }
+        cudaEventRecord(d.ev1, d.stream);
+        cudaMemcpyAsync(words.data(), d_out, 32 * (size_t)n, cudaMemcpyDeviceToHost, d.stream);
+        if ((e = cudaStreamSynchronize(d.stream)) != cudaSuccess) { set_err(ctx, cudaGetErrorString(e)); break; }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, d.ev0, d.ev1);
+        *kernel_ms = ms;
+        for (size_t i = 0; i < words.size(); i++) store_be32(out + 32 * (size_t)m_lo + 4 * i, words[i]);
+        rc = UPOW_OK;
+    } while (0);
+    cudaFree(d_data); cudaFree(d_off); cudaFree(d_out);
+    return rc;
+}
+}  // namespace
+
+extern "C" int upow_sha256_batch(upow_ctx* ctx, uint32_t n, const uint8_t* data, const uint64_t* offsets, uint8_t* out,
+                                 upow_result* stats) {
+    if (!ctx || (n && (!offsets || !out))) return UPOW_E_ARG;
+    try {
+        std::lock_guard<std::mutex> g(ctx->api_mu);
+        if (stats) memset(stats, 0, sizeof *stats);
+        if (n == 0) return UPOW_OK;
+        for (uint32_t i = 0; i < n; i++)
+            if (offsets[i + 1] < offsets[i]) { set_err(ctx, "upow_sha256_batch: offsets must be non-decreasing"); return UPOW_E_ARG; }
+        if (offsets[n] > offsets[0] && !data) return UPOW_E_ARG;
+        const double t_begin = now_s();
+        const int n_dev = (int)ctx->devs.size();
+        std::vector<uint32_t> cut(n_dev + 1);
+        for (int i = 0; i <= n_dev; i++) cut[i] = (uint32_t)((uint64_t)n * i / n_dev);
+        std::vector<int> rcs(n_dev, UPOW_OK);
+        std::vector<double> ms(n_dev, 0.0);
+        auto worker = [&](int di) {
+            rcs[di] = sha_batch_on_device(ctx, ctx->devs[di], data, offsets, cut[di], cut[di + 1], out, &ms[di]);
         };
         if (n_dev == 1) worker(0);
         else {
