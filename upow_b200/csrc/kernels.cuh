@@ -232,8 +232,8 @@ __global__ void __launch_bounds__(256) search_kernel(const __grid_constant__ Sea
 // Contiguous search, hand-specialised per layout with explicit pipe assignment (hot_loop.h).
 // Same work decomposition and hit protocol as search_kernel above; Tn selects how much of the
 // integer work is issued on the fma pipe.
-template <int LAYOUT, int MODE, class Tn, int MINB>
-__global__ void __launch_bounds__(256, MINB) search_kernel_tuned(const __grid_constant__ SearchArgs A) {
+template <int LAYOUT, int MODE, class Tn, int MINB, int BLOCK = 256>
+__global__ void __launch_bounds__(BLOCK, MINB) search_kernel_tuned(const __grid_constant__ SearchArgs A) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     uint32_t done = 0;

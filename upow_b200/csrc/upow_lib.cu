@@ -188,13 +188,17 @@ typedef void (*SearchFn)(const SearchArgs);
 struct Variant {
     const char* name;
     SearchFn fn[2][2];  // [layout-1][mode]
+    int block;          // threads per block (the kernels are warp-granular, any multiple of 32 works)
 };
 #define UPOW_PLAIN_VARIANT(NAME)                                                                     \
     { NAME, { { search_kernel<LAYOUT_V1, MODE_MIN, 1>, search_kernel<LAYOUT_V1, MODE_ENUM, 1> },      \
-              { search_kernel<LAYOUT_V2, MODE_MIN, 1>, search_kernel<LAYOUT_V2, MODE_ENUM, 1> } } }
+              { search_kernel<LAYOUT_V2, MODE_MIN, 1>, search_kernel<LAYOUT_V2, MODE_ENUM, 1> } }, 256 }
 #define UPOW_TUNED_VARIANT(NAME, TN, MINB)                                                           \
     { NAME, { { search_kernel_tuned<LAYOUT_V1, MODE_MIN, TN, MINB>, search_kernel_tuned<LAYOUT_V1, MODE_ENUM, TN, MINB> }, \
-              { search_kernel_tuned<LAYOUT_V2, MODE_MIN, TN, MINB>, search_kernel_tuned<LAYOUT_V2, MODE_ENUM, TN, MINB> } } }
+              { search_kernel_tuned<LAYOUT_V2, MODE_MIN, TN, MINB>, search_kernel_tuned<LAYOUT_V2, MODE_ENUM, TN, MINB> } }, 256 }
+#define UPOW_TUNED_VARIANT_B(NAME, TN, MINB, BLOCK)                                                  \
+    { NAME, { { search_kernel_tuned<LAYOUT_V1, MODE_MIN, TN, MINB, BLOCK>, search_kernel_tuned<LAYOUT_V1, MODE_ENUM, TN, MINB, BLOCK> }, \
+              { search_kernel_tuned<LAYOUT_V2, MODE_MIN, TN, MINB, BLOCK>, search_kernel_tuned<LAYOUT_V2, MODE_ENUM, TN, MINB, BLOCK> } }, BLOCK }
 #define TN(...) Tune<__VA_ARGS__>
 const Variant VARIANTS[] = {
     UPOW_PLAIN_VARIANT("plain: nvcc-chosen pipes"),
@@ -210,6 +214,7 @@ const Variant VARIANTS[] = {
     UPOW_TUNED_VARIANT("add, 7-add, shr via IMAD.HI on 2/4 words", TN(1, 2, 0, 0, 0, 0, 0, 2), 3),
     UPOW_TUNED_VARIANT("add, 7-add, shr via IMAD.WIDE on 2/4 words", TN(1, 1, 0, 0, 0, 0, 0, 2), 3),
     UPOW_TUNED_VARIANT("add only, 7-add rounds, 4 blocks/SM", TN(1, 0, 0, 0, 0, 0, 0), 4),
+    UPOW_TUNED_VARIANT_B("add only, 7-add, 128-thread blocks x7 (28 warps/SM)", TN(1, 0, 0, 0, 0, 0, 0), 7, 128),
 };
 constexpr int N_VARIANTS = sizeof(VARIANTS) / sizeof(VARIANTS[0]);
 constexpr int DEFAULT_VARIANT = 8;
@@ -217,7 +222,7 @@ constexpr int DEFAULT_VARIANT = 8;
 cudaError_t launch_search(const Device& d, const SearchArgs& a, int mode, int variant) {
     SearchFn fn = VARIANTS[variant].fn[a.tail.layout == LAYOUT_V1 ? 0 : 1][mode == MODE_MIN ? 0 : 1];
     int grid = d.variant_grid[variant];
-    fn<<<grid, 256, 0, d.stream>>>(a);
+    fn<<<grid, VARIANTS[variant].block, 0, d.stream>>>(a);
     return cudaGetLastError();
 }
 template <int MODE>
@@ -234,7 +239,7 @@ int init_variant_grids(upow_ctx* ctx, Device& d) {
     static_assert(N_VARIANTS <= 16, "variant_grid too small");
     for (int v = 0; v < N_VARIANTS; v++) {
         int per_sm = 0;
-        CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, VARIANTS[v].fn[0][1], 256, 0));
+        CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, VARIANTS[v].fn[0][1], VARIANTS[v].block, 0));
         if (per_sm < 1) per_sm = 1;
         d.variant_grid[v] = d.sm_count * per_sm;
     }
@@ -260,7 +265,7 @@ int run_contiguous(upow_ctx* ctx, Device& d, const Tail& tail, const Rule& rule,
     a.h_count = h_hi - a.h_lo;
     // items of up to 64 H values; small ranges get smaller items so every warp has work
     uint32_t hc = 64;
-    const uint32_t n_warps = d.variant_grid[ctx->variant] * 8;
+    const uint32_t n_warps = d.variant_grid[ctx->variant] * (VARIANTS[ctx->variant].block / 32);
     while (hc > 1 && (uint64_t)((a.h_count + hc - 1) / hc) * 2048 < 4ull * n_warps) hc >>= 1;
     a.hc = hc;
     a.n_items = ((a.h_count + hc - 1) / hc) * 2048;
