@@ -177,7 +177,7 @@ def load_sass_counts():
 
 def roofline(kernel_ghs, sm_mhz, sm_count, rates, sass):
     """H_peak = SMs * f / max(N_alu/R_alu, N_fma/R_fma, N_total/R_issue)  (SURVEY 8(d))."""
-    if not sass or not rates or not sm_mhz:
+    if not sass or not rates or not sm_mhz or not sass.get("bench_kernel") or sass["bench_kernel"] not in sass.get("kernels", {}):
         return {"bound": "int_alu", "achieved": kernel_ghs, "peak": None, "unit": UNIT, "frac": None, "traffic": None}
     k = sass["kernels"][sass["bench_kernel"]]
     n_alu, n_fma, n_total = k["alu_per_hash"], k["fma_per_hash"], k["total_per_hash"]

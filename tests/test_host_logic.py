@@ -263,3 +263,81 @@ def test_miner_mirror_exhaustion_raises_overflow(monkeypatch):
     with pytest.raises(OverflowError):  # the reference: nonce.to_bytes(4, ...) at 2**32, miner.py:87
         miner.mine_block(0, 1, O.t0_mining_params(4.0))
     miner.set_context(None)
+
+
+def test_committed_sass_counts_match_the_built_library():
+    """profiles/sass_counts.json (what bench.py's roofline uses) is in step with libupow_b200.so."""
+    import json
+    import shutil
+    import upow_b200
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not installed")
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import sass_count
+    committed = json.load(open(os.path.join(ROOT, "profiles", "sass_counts.json")))
+    name = committed["bench_kernel"]
+    assert name and name in committed["kernels"]
+    upow_b200.load()
+    live = sass_count.analyse(upow_b200.library_path(), r"search_kernel_tunedILi1ELi1ENS_4TuneILi1ELi0ELi0ELi0ELi0ELi0ELi0ELi4EEELi3ELi256")
+    assert len(live) == 1
+    (r,) = live.values()
+    k = committed["kernels"][name]
+    assert (r["total"], r["pipes"].get("alu", 0), r["pipes"].get("fma", 0)) == \
+           (k["total_per_hash"], k["alu_per_hash"], k["fma_per_hash"])
+    # the generic model of SURVEY 8(d): between the folded estimate -10 % and 1386 + pipe-move overhead
+    assert 1100 < k["total_per_hash"] < 1600 and k["alu_per_hash"] < 1000
+
+
+def test_miner_main_round_structure_with_multiplier(monkeypatch, capsys):
+    """main(): fetch get_mining_info, race UPOW_TEMPLATES templates, POST the winner, start the next round
+    (miner.py:126-156 with the optional template multiplier)."""
+    import types
+    from upow_b200 import miner
+
+    class AnyCtx(_FakeContext):
+        def search_any(self, templates, max_nonce=0):
+            for n in range(1 << 20):
+                for i, (prefix, prev, n_int, cc) in enumerate(templates):
+                    h = hashlib.sha256(prefix + n.to_bytes(4, "little")).hexdigest()
+                    if h.startswith(prev.hex()[-n_int:]) and (cc == 16 or int(h[n_int], 16) < cc):
+                        class S:
+                            hashes_done, elapsed_s = 1, 0.0
+                        return 0, i, n, bytes.fromhex(h), S()
+            return 1, 0, 0, b"", None
+
+    info = {"difficulty": 2.5, "last_block": {"hash": O.T0_PREV_HASH, "id": 41, "timestamp": 1_699_999_990},
+            "pending_transactions_hashes": sorted(hashlib.sha256(b"t%d" % i).hexdigest() for i in range(2))}
+    posted, gets = [], []
+
+    class Resp:
+        def __init__(self, payload):
+            self.payload = payload
+
+        def json(self):
+            return self.payload
+
+    def fake_get(url, timeout=None):
+        gets.append(url)
+        if len(gets) > 1:
+            raise KeyboardInterrupt          # end the endless round loop of main()
+        return Resp({"ok": True, "result": info})
+
+    fake = types.ModuleType("requests")
+    fake.get = fake_get
+    fake.post = lambda url, json=None, timeout=None: (posted.append((url, json)), Resp({"ok": True}))[1]
+    monkeypatch.setitem(sys.modules, "requests", fake)
+    monkeypatch.setenv("UPOW_TEMPLATES", "12")
+    monkeypatch.setattr(sys, "argv", ["miner.py", O.T0_ADDRESS_V1, "1", "http://node.example:3006/"])
+    monkeypatch.setattr(miner, "timestamp", lambda: 1_700_000_000)
+    miner.set_context(AnyCtx())
+    with pytest.raises(KeyboardInterrupt):
+        miner.main()
+    miner.set_context(None)
+    assert gets[0] == "http://node.example:3006/get_mining_info" and len(posted) == 1
+    url, body = posted[0]
+    assert url.endswith("/push_block") and body["block_no"] == 42
+    assert O.node_check_block_is_valid(body["block_content"], 2.5, info["last_block"])
+    raw = bytes.fromhex(body["block_content"])
+    assert 1_699_999_990 < int.from_bytes(raw[-10:-6], "little") <= 1_700_000_000
+    assert raw[96:128].hex() == O.calculate_merkle_root(body["txs"])
+    assert "BLOCK MINED" in capsys.readouterr().out

@@ -102,17 +102,23 @@ def mine_block(start_nonce: int = 0, nonce_increment: int = 1, mining_params: di
         return None  # stale or cancelled: nothing is submitted (miner.py:96-98)
 
     candidate = with_timestamp(prefix, res.timestamp) + res.nonce.to_bytes(4, ENDIAN)
-    print(candidate.hex())
+    _submit(requests, candidate.hex(), tx_hashes, last_block["id"] + 1)
+    exit()
+
+
+def _submit(requests, block_content_hex: str, tx_hashes, block_no: int):
+    """miner.py:99-113: print the candidate, POST it to <node>/push_block, print the reply."""
+    print(block_content_hex)
     print(",".join(tx_hashes))
     response = requests.post(
         _node_url() + "push_block",
-        json={"block_content": candidate.hex(), "txs": tx_hashes, "block_no": last_block["id"] + 1},
+        json={"block_content": block_content_hex, "txs": tx_hashes, "block_no": block_no},
         timeout=20 + int((len(tx_hashes) or 1) / 3),
     )
     print(result := response.json())
     if result["ok"]:
         print("BLOCK MINED\n\n")
-    exit()
+    return result
 
 
 def mining_worker(start_nonce: int, nonce_increment: int, mining_params: dict):
@@ -135,10 +141,32 @@ def main():
             except Exception as e:  # the reference retries forever, once a second
                 print(e)
                 time.sleep(1)
+        # optional extras beyond the reference (both off by default so the CLI behaves like miner.py):
+        #   UPOW_TEMPLATES=N     race N templates of this reply (timestamps x transaction subsets), multiplier.py
+        #   UPOW_STALE_POLL_S=s  abandon the search as soon as the node's tip moves, stale.py
+        n_templates = int(os.environ.get("UPOW_TEMPLATES", "1"))
+        poll_s = float(os.environ.get("UPOW_STALE_POLL_S", "0"))
+        watcher = None
+        if poll_s > 0:
+            from . import stale
+            watcher = stale.StaleWatcher(get_context(), info["last_block"].get("id", 0),
+                                         stale.http_tip_fetcher(_node_url()), poll_s)
+            watcher.__enter__()
         try:
-            mine_block(0, 1, info)
+            if n_templates > 1:
+                from . import multiplier
+                out = multiplier.mine_any(get_context(), info, sys.argv[1], timestamp(), n_templates)
+                if out is not None:
+                    _submit(requests, out["block_content"], out["txs"], out["block_no"])
+            else:
+                mine_block(0, 1, info)
         except OverflowError:
             continue  # nonce space exhausted: fetch a fresh template (new timestamp)
+        except SystemExit:
+            continue  # the reference's worker exits after a submit and the parent starts the next round
+        finally:
+            if watcher is not None:
+                watcher.__exit__(None, None, None)
 
 
 if __name__ == "__main__":
