@@ -378,6 +378,8 @@ def main():
                    "parallelism": f"{n_total_gpus} independent nonce-space shards, no collective",
                    "launcher": "torchrun, one rank per GPU" if world > 1 else "single process",
                    "l2": "flushed between steps (256 MiB memset inside the timed region); the kernel reads no HBM inputs",
+                   "timing": "value: host clock around the K steps, every step ends in a stream synchronise, barrier on both "
+                             "sides, max over ranks; roofline.achieved: CUDA events on the library's stream around each kernel",
                    "device": info.name.decode(), "grid_blocks": info.search_grid_blocks},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // max(args.steps, 1),
                 "d2h_bytes_per_step": d2h // max(args.steps, 1)},
