@@ -90,12 +90,18 @@ def test_strided_search_matches_reference_worker_layout(gpu_ctx, version):
     prefix = O.t0_prefix(4.6, version)
     rule = make_rule(4.6, O.T0_PREV_HASH)
     _set(gpu_ctx, 0, prefix, rule)
-    for start, inc in [(0, 2), (1, 2), (3, 8), (7, 8), (5, 96), (12345, 1000), (0, 65536), (17, 65537), (2, 3)]:
-        rc, res = gpu_ctx.search_min(0, start, inc)
-        want, _ = c_oracle.min_valid_nonce(prefix, rule, start, inc)
-        assert (rc == 0 and res.nonce == want) if want is not None else rc == 1, (start, inc)
-        if want is not None:
-            assert (res.nonce - start) % inc == 0
+    default_variant = gpu_ctx.variant
+    try:
+        for variant in (default_variant, 0):      # pipe-assigned build and the plain-CUDA build of the strided kernel
+            gpu_ctx.variant = variant
+            for start, inc in [(0, 2), (1, 2), (3, 8), (7, 8), (5, 96), (12345, 1000), (0, 65536), (17, 65537), (2, 3)]:
+                rc, res = gpu_ctx.search_min(0, start, inc)
+                want, _ = c_oracle.min_valid_nonce(prefix, rule, start, inc)
+                assert (rc == 0 and res.nonce == want) if want is not None else rc == 1, (variant, start, inc)
+                if want is not None:
+                    assert (res.nonce - start) % inc == 0
+    finally:
+        gpu_ctx.variant = default_variant
 
 
 def test_start_nonce_and_max_nonce_bounds(gpu_ctx, sweep_fixture):

@@ -67,6 +67,8 @@ struct StridedArgs {
     uint32_t* out;
     uint32_t cap;
     uint32_t pad;
+    Opaque q;           // used by the TUNED build only
+    V2Consts v2;
 };
 
 __constant__ uint32_t K_DEV[64];
@@ -288,8 +290,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) search_kernel_tuned(const __grid_
 // Strided search (the reference's residue-class worker layout, miner.py:139-148):
 // nonce_i = start + i*stride.  Nothing is hoisted: all 64 rounds run per nonce from the
 // midstate, which also makes this kernel an independent cross-check of search_kernel.
-template <int LAYOUT, int MODE>
-__global__ void __launch_bounds__(256) search_strided_kernel(const __grid_constant__ StridedArgs A) {
+// TUNED = true runs the same pipe-assigned rounds as search_kernel_tuned instead (the per-lane set-up of the
+// 138-byte layout is then redone for every nonce, because W1 changes with every step).
+using StridedTune = Tune<1, 0, 0, 0, 0, 0, 0>;
+template <int LAYOUT, int MODE, bool TUNED = false>
+__global__ void __launch_bounds__(256, TUNED ? 3 : 1) search_strided_kernel(const __grid_constant__ StridedArgs A) {
     const uint32_t lane = threadIdx.x & 31;
     uint32_t done = 0;
     for (;;) {
@@ -303,6 +308,20 @@ __global__ void __launch_bounds__(256) search_strided_kernel(const __grid_consta
             const unsigned long long i = i0 + (unsigned long long)k * 32u + lane;
             const bool live = i < A.n_steps;
             const uint32_t nonce = (uint32_t)(A.start + i * A.stride);
+            if (TUNED) {
+                uint32_t a64t;
+                if (LAYOUT == LAYOUT_V1) {
+                    const V1Lane s = v1_lane_setup(A.tail, nonce & 0xffffu);
+                    a64t = v1_nonce_a64<StridedTune>(s, v1_w2(nonce >> 16), A.q);
+                } else {
+                    a64t = v2_nonce_a64<StridedTune>(A.v2, bswap32(nonce), A.q);
+                }
+                const bool hit_t = live && (addu<true>(a64t, A.rule.sub0, A.q) < A.rule.range0);
+                if (__ballot_sync(0xffffffffu, hit_t)) {
+                    if (hit_t) report_hit<MODE>(A.tail, A.rule, A.start, 1ull << 32, nonce, A.res, A.out, A.cap);
+                }
+                continue;
+            }
             uint32_t w[16];
             if (LAYOUT == LAYOUT_V1) {
                 w[0] = A.tail.w[0];

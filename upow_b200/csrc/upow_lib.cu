@@ -48,6 +48,7 @@ struct Device {
     int grid_blocks = 0;   // persistent grid of the strided kernel
     int variant_grid[16] = {0};
     int batch_grid = 0;
+    int strided_tuned_grid = 0;
     cudaDeviceProp prop;
     cudaStream_t stream = nullptr, ctrl = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -225,12 +226,18 @@ cudaError_t launch_search(const Device& d, const SearchArgs& a, int mode, int va
     fn<<<grid, VARIANTS[variant].block, 0, d.stream>>>(a);
     return cudaGetLastError();
 }
+// variant 0 keeps the plain-CUDA strided kernel (independent implementation); every other variant
+// uses the pipe-assigned build
 template <int MODE>
-cudaError_t launch_strided(const Device& d, const StridedArgs& a) {
-    if (a.tail.layout == LAYOUT_V1)
-        search_strided_kernel<LAYOUT_V1, MODE><<<d.grid_blocks, 256, 0, d.stream>>>(a);
-    else
-        search_strided_kernel<LAYOUT_V2, MODE><<<d.grid_blocks, 256, 0, d.stream>>>(a);
+cudaError_t launch_strided(const Device& d, const StridedArgs& a, bool tuned) {
+    const int grid = tuned ? d.strided_tuned_grid : d.grid_blocks;
+    if (a.tail.layout == LAYOUT_V1) {
+        if (tuned) search_strided_kernel<LAYOUT_V1, MODE, true><<<grid, 256, 0, d.stream>>>(a);
+        else search_strided_kernel<LAYOUT_V1, MODE, false><<<grid, 256, 0, d.stream>>>(a);
+    } else {
+        if (tuned) search_strided_kernel<LAYOUT_V2, MODE, true><<<grid, 256, 0, d.stream>>>(a);
+        else search_strided_kernel<LAYOUT_V2, MODE, false><<<grid, 256, 0, d.stream>>>(a);
+    }
     return cudaGetLastError();
 }
 
@@ -246,6 +253,8 @@ int init_variant_grids(upow_ctx* ctx, Device& d) {
     int per_sm = 0;
     CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, batch_kernel<LAYOUT_V1>, 256, 0));
     d.batch_grid = d.sm_count * (per_sm < 1 ? 1 : per_sm);
+    CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, search_strided_kernel<LAYOUT_V1, MODE_MIN, true>, 256, 0));
+    d.strided_tuned_grid = d.sm_count * (per_sm < 1 ? 1 : per_sm);
     return UPOW_OK;
 }
 
@@ -315,7 +324,8 @@ int run_strided(upow_ctx* ctx, Device& d, const Tail& tail, const Rule& rule, ui
     a.stride = stride;
     a.n_steps = s_hi - s_lo;
     uint32_t ic = 64;
-    const uint32_t n_warps = d.grid_blocks * 8;
+    const bool tuned = ctx->variant != 0;
+    const uint32_t n_warps = (tuned ? d.strided_tuned_grid : d.grid_blocks) * 8;
     while (ic > 1 && (a.n_steps + 32ull * ic - 1) / (32ull * ic) < 4ull * n_warps) ic >>= 1;
     a.ic = ic;
     a.n_items = (uint32_t)((a.n_steps + 32ull * ic - 1) / (32ull * ic));
@@ -328,7 +338,9 @@ int run_strided(upow_ctx* ctx, Device& d, const Tail& tail, const Rule& rule, ui
     *d.h_res = init;
     CU_TRY(ctx, cudaMemcpyAsync(d.d_res, d.h_res, sizeof(DevResult), cudaMemcpyHostToDevice, d.stream));
     CU_TRY(ctx, cudaEventRecord(d.ev0, d.stream));
-    CU_TRY(ctx, launch_strided<MODE_MIN>(d, a));
+    fill_opaque(&a.q);
+    if (tail.layout == LAYOUT_V2) prepare_v2_consts(tail, &a.v2);
+    CU_TRY(ctx, launch_strided<MODE_MIN>(d, a, tuned));
     CU_TRY(ctx, cudaEventRecord(d.ev1, d.stream));
     int st = wait_event(ctx, d, d.ev1, deadline);
     if (st < 0) return st;
