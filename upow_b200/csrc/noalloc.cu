@@ -108,7 +108,12 @@ int setup_current_device(PerDevice& pd) {
 
 }  // namespace
 
-extern "C" const char* upow_noalloc_last_error(void) { return g_err.c_str(); }
+extern "C" const char* upow_noalloc_last_error(void) {
+    thread_local std::string copy;   // per-thread copy: another thread may rewrite g_err at any time
+    std::lock_guard<std::mutex> g(g_err_mu);
+    copy = g_err;
+    return copy.c_str();
+}
 
 extern "C" int upow_sweep_noalloc(int device, const uint8_t* prefix, int prefix_len, const uint8_t* prev_hash32,
                                   int n_int, int charset_count, uint64_t nonce_lo, uint64_t nonce_hi,

@@ -402,8 +402,16 @@ bool host_verify(const Prepared& p, uint32_t nonce, const uint8_t dev_digest[32]
 extern "C" const char* upow_version(void) { return "upow_b200 0.1 (sm_100a)"; }
 
 extern "C" const char* upow_last_error(const upow_ctx* ctx) {
-    if (ctx) return ctx->err.c_str();
-    return g_init_error.c_str();
+    // a per-thread copy: the string inside the context may be rewritten by another thread at any time
+    thread_local std::string copy;
+    if (ctx) {
+        std::lock_guard<std::mutex> g(const_cast<upow_ctx*>(ctx)->err_mu);
+        copy = ctx->err;
+    } else {
+        std::lock_guard<std::mutex> g(g_init_mu);
+        copy = g_init_error;
+    }
+    return copy.c_str();
 }
 
 extern "C" int upow_init(int n_devices, const int* device_ids, upow_ctx** out_ctx) {
