@@ -301,6 +301,13 @@ def test_argument_errors(gpu_ctx):
         gpu_ctx.search_min(63)          # slot never set
     with pytest.raises(upow_b200.UpowError):
         gpu_ctx.search_min(0, 0, 0)     # stride 0
+    good = (O.t0_prefix(4.0), bytes(32), 4, 16)
+    for bad in ((b"x" * 90, bytes(32), 4, 16), (O.t0_prefix(4.0), bytes(32), 4, 17), (O.t0_prefix(4.0), bytes(32), 64, 8)):
+        with pytest.raises(upow_b200.UpowError) as e:
+            gpu_ctx.search_batch([good] * 3 + [bad])
+        assert e.value.code == -1 and "template 3" in str(e.value)
+        with pytest.raises(upow_b200.UpowError):
+            gpu_ctx.search_any([bad])
 
 
 def test_linearity_of_hash_counts(gpu_ctx):

@@ -853,24 +853,33 @@ namespace {
 int prepare_templates(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates, std::vector<Prepared>* prep,
                       const char* who) {
     prep->resize(n_templates);
-    for (uint32_t i = 0; i < n_templates; i++) {
-        Slot s;
-        s.used = true;
-        if (templates[i].prefix_len != 134 && templates[i].prefix_len != 104) {
-            set_err(ctx, std::string(who) + ": template " + std::to_string(i) + ": prefix_len not 104/134");
-            return UPOW_E_ARG;
+    std::atomic<int> rc{UPOW_OK};
+    std::atomic<uint32_t> bad{0};
+    auto range = [&](uint32_t lo, uint32_t hi) {
+        for (uint32_t i = lo; i < hi && rc.load() == UPOW_OK; i++) {
+            Slot s;
+            s.used = true;
+            if (templates[i].prefix_len != 134 && templates[i].prefix_len != 104) { bad = i; rc = UPOW_E_ARG; return; }
+            memcpy(s.prefix, templates[i].prefix, sizeof s.prefix);
+            s.prefix_len = (int)templates[i].prefix_len;
+            memcpy(s.prev_hash, templates[i].prev_hash, 32);
+            s.n_int = templates[i].n_int;
+            s.charset_count = templates[i].charset_count;
+            if (!prepare_slot(s, 0, &(*prep)[i])) { bad = i; rc = UPOW_E_ARG; return; }
         }
-        memcpy(s.prefix, templates[i].prefix, sizeof s.prefix);
-        s.prefix_len = (int)templates[i].prefix_len;
-        memcpy(s.prev_hash, templates[i].prev_hash, 32);
-        s.n_int = templates[i].n_int;
-        s.charset_count = templates[i].charset_count;
-        if (!prepare_slot(s, 0, &(*prep)[i])) {
-            set_err(ctx, std::string(who) + ": template " + std::to_string(i) + ": bad rule");
-            return UPOW_E_ARG;
-        }
+    };
+    // midstates of thousands of templates: spread over a few host threads
+    const uint32_t n_thr = n_templates >= 1024 ? std::min<uint32_t>(8, std::max(1u, std::thread::hardware_concurrency())) : 1;
+    if (n_thr == 1) range(0, n_templates);
+    else {
+        std::vector<std::thread> th;
+        for (uint32_t t = 0; t < n_thr; t++)
+            th.emplace_back(range, (uint32_t)((uint64_t)n_templates * t / n_thr), (uint32_t)((uint64_t)n_templates * (t + 1) / n_thr));
+        for (auto& t : th) t.join();
     }
-    return UPOW_OK;
+    if (rc.load() != UPOW_OK)
+        set_err(ctx, std::string(who) + ": template " + std::to_string(bad.load()) + ": prefix_len not 104/134 or bad rule");
+    return rc.load();
 }
 }  // namespace
 
@@ -907,6 +916,21 @@ extern "C" int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow
         auto worker = [&](int di) {
             rcs[di] = run_batch_on_device(ctx, ctx->devs[di], jobs[di], max_nonce, &best[di], &dig[di], &hashes[di],
                                           &ms[di], &launches[di]);
+            if (rcs[di] != UPOW_OK) return;
+            // results of this device's templates, each cross-checked with the host SHA-256
+            for (size_t k = 0; k < owner[di].size(); k++) {
+                const uint32_t i = owner[di][k];
+                memset(&results[i], 0, sizeof results[i]);
+                if (best[di][k] == ~0ull) continue;
+                results[i].found = 1;
+                results[i].nonce = (uint32_t)best[di][k];
+                for (int w = 0; w < 8; w++) store_be32(results[i].digest + 4 * w, dig[di][k * 8 + w]);
+                if (!host_verify(prep[i], results[i].nonce, results[i].digest)) {
+                    set_err(ctx, "batch result " + std::to_string(i) + " failed the host cross-check");
+                    rcs[di] = UPOW_E_INTERNAL;
+                    return;
+                }
+            }
         };
         if (n_dev == 1) worker(0);
         else {
@@ -922,18 +946,6 @@ extern "C" int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow
                 stats->hashes_done += hashes[di];
                 stats->kernel_ms = std::max(stats->kernel_ms, ms[di]);
                 stats->launches += launches[di];
-            }
-            for (size_t k = 0; k < owner[di].size(); k++) {
-                const uint32_t i = owner[di][k];
-                memset(&results[i], 0, sizeof results[i]);
-                if (best[di][k] == ~0ull) continue;
-                results[i].found = 1;
-                results[i].nonce = (uint32_t)best[di][k];
-                for (int w = 0; w < 8; w++) store_be32(results[i].digest + 4 * w, dig[di][k * 8 + w]);
-                if (!host_verify(prep[i], results[i].nonce, results[i].digest)) {
-                    set_err(ctx, "batch result " + std::to_string(i) + " failed the host cross-check");
-                    return UPOW_E_INTERNAL;
-                }
             }
         }
         if (stats) stats->elapsed_s = now_s() - t_begin;
