@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(256) search_kernel(const __grid_constant__ Sea
 // Contiguous search, hand-specialised per layout with explicit pipe assignment (hot_loop.h).
 // Same work decomposition and hit protocol as search_kernel above; Tn selects how much of the
 // integer work is issued on the fma pipe.
-template <int LAYOUT, int MODE, class Tn, int MINB, int BLOCK = 256>
+template <int LAYOUT, int MODE, class Tn, int MINB, int BLOCK = 256, int NPT = 1>
 __global__ void __launch_bounds__(BLOCK, MINB) search_kernel_tuned(const __grid_constant__ SearchArgs A) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -261,20 +261,30 @@ __global__ void __launch_bounds__(BLOCK, MINB) search_kernel_tuned(const __grid_
 
         if (LAYOUT == LAYOUT_V1) {
             const V1Lane s = v1_lane_setup(A.tail, L);
-            for (uint32_t H = h0; H < h_end; H++) {
-                const uint32_t a64 = v1_nonce_a64<Tn>(s, v1_w2(H), A.q);
-                const bool hit = addu<Tn::ADD != 0>(a64, A.rule.sub0, A.q) < A.rule.range0;
-                if (__ballot_sync(0xffffffffu, hit)) {
-                    if (hit) report_hit<MODE>(A.tail, A.rule, A.nonce_lo, A.nonce_hi, (H << 16) | L, A.res, A.out, A.cap);
+            for (uint32_t H = h0; H < h_end; H += NPT) {
+                uint32_t a64[NPT];
+#pragma unroll
+                for (int j = 0; j < NPT; j++) a64[j] = v1_nonce_a64<Tn>(s, v1_w2(H + j), A.q);   // independent chains
+#pragma unroll
+                for (int j = 0; j < NPT; j++) {
+                    const bool hit = addu<Tn::ADD != 0>(a64[j], A.rule.sub0, A.q) < A.rule.range0 && (NPT == 1 || H + j < h_end);
+                    if (__ballot_sync(0xffffffffu, hit)) {
+                        if (hit) report_hit<MODE>(A.tail, A.rule, A.nonce_lo, A.nonce_hi, ((H + j) << 16) | L, A.res, A.out, A.cap);
+                    }
                 }
             }
         } else {
             const uint32_t lsw = v2_w10_from_L(L);
-            for (uint32_t H = h0; H < h_end; H++) {
-                const uint32_t a64 = v2_nonce_a64<Tn>(A.v2, lsw | v2_w10_from_H(H), A.q);
-                const bool hit = addu<Tn::ADD != 0>(a64, A.rule.sub0, A.q) < A.rule.range0;
-                if (__ballot_sync(0xffffffffu, hit)) {
-                    if (hit) report_hit<MODE>(A.tail, A.rule, A.nonce_lo, A.nonce_hi, (H << 16) | L, A.res, A.out, A.cap);
+            for (uint32_t H = h0; H < h_end; H += NPT) {
+                uint32_t a64[NPT];
+#pragma unroll
+                for (int j = 0; j < NPT; j++) a64[j] = v2_nonce_a64<Tn>(A.v2, lsw | v2_w10_from_H(H + j), A.q);
+#pragma unroll
+                for (int j = 0; j < NPT; j++) {
+                    const bool hit = addu<Tn::ADD != 0>(a64[j], A.rule.sub0, A.q) < A.rule.range0 && (NPT == 1 || H + j < h_end);
+                    if (__ballot_sync(0xffffffffu, hit)) {
+                        if (hit) report_hit<MODE>(A.tail, A.rule, A.nonce_lo, A.nonce_hi, ((H + j) << 16) | L, A.res, A.out, A.cap);
+                    }
                 }
             }
         }

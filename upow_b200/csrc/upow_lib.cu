@@ -200,6 +200,9 @@ struct Variant {
 #define UPOW_TUNED_VARIANT_B(NAME, TN, MINB, BLOCK)                                                  \
     { NAME, { { search_kernel_tuned<LAYOUT_V1, MODE_MIN, TN, MINB, BLOCK>, search_kernel_tuned<LAYOUT_V1, MODE_ENUM, TN, MINB, BLOCK> }, \
               { search_kernel_tuned<LAYOUT_V2, MODE_MIN, TN, MINB, BLOCK>, search_kernel_tuned<LAYOUT_V2, MODE_ENUM, TN, MINB, BLOCK> } }, BLOCK }
+#define UPOW_TUNED_VARIANT_N(NAME, TN, MINB, BLOCK, NPT)                                             \
+    { NAME, { { search_kernel_tuned<LAYOUT_V1, MODE_MIN, TN, MINB, BLOCK, NPT>, search_kernel_tuned<LAYOUT_V1, MODE_ENUM, TN, MINB, BLOCK, NPT> }, \
+              { search_kernel_tuned<LAYOUT_V2, MODE_MIN, TN, MINB, BLOCK, NPT>, search_kernel_tuned<LAYOUT_V2, MODE_ENUM, TN, MINB, BLOCK, NPT> } }, BLOCK }
 #define TN(...) Tune<__VA_ARGS__>
 const Variant VARIANTS[] = {
     UPOW_PLAIN_VARIANT("plain: nvcc-chosen pipes"),
@@ -216,6 +219,7 @@ const Variant VARIANTS[] = {
     UPOW_TUNED_VARIANT("add, 7-add, shr via IMAD.WIDE on 2/4 words", TN(1, 1, 0, 0, 0, 0, 0, 2), 3),
     UPOW_TUNED_VARIANT("add only, 7-add rounds, 4 blocks/SM", TN(1, 0, 0, 0, 0, 0, 0), 4),
     UPOW_TUNED_VARIANT_B("add only, 7-add, 128-thread blocks x7 (28 warps/SM)", TN(1, 0, 0, 0, 0, 0, 0), 7, 128),
+    UPOW_TUNED_VARIANT_N("add only, 7-add, 2 nonces per lane, 128-thread blocks x4", TN(1, 0, 0, 0, 0, 0, 0), 4, 128, 2),
 };
 constexpr int N_VARIANTS = sizeof(VARIANTS) / sizeof(VARIANTS[0]);
 constexpr int DEFAULT_VARIANT = 8;
