@@ -454,6 +454,20 @@ __global__ void __launch_bounds__(256, 3) batch_kernel(const __grid_constant__ B
     if (lane == 0 && done) atomicAdd(&A.res->items_done, (unsigned long long)done);
 }
 
+// Fully unrolled generic compression (no folded words): verifier and batched hashing.
+__device__ __forceinline__ void compress_unrolled(uint32_t st[8], uint32_t (&w)[16]) {
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+#pragma unroll
+    for (int t = 0; t < 64; t++) {
+        if (t >= 16)
+            w[t & 15] = w[t & 15] + small_sigma0(w[(t + 1) & 15]) + w[(t + 9) & 15] + small_sigma1(w[(t + 14) & 15]);
+        uint32_t t1 = h + big_sigma1(e) + ch(e, f, g) + (Kc(t) + w[t & 15]);
+        uint32_t t2 = big_sigma0(a) + maj(a, b, c);
+        h = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
+    }
+    st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
+}
+
 // ---------------------------------------------------------------------------------------
 // Batch block verifier: check_block_is_valid (upow/manager.py:130-151) for many
 // finished blocks at once -- what chain sync does one block at a time (upow/node/main.py:97-150).
@@ -503,7 +517,7 @@ __global__ void __launch_bounds__(VERIFY_THREADS) verify_kernel(const VerifyReco
                 if (b == n_blocks - 1 && i == 15) v = len * 8;
                 w[i] = v;
             }
-            compress_rolled(st, w, K_DEV);
+            compress_unrolled(st, w);
         }
         uint32_t prev[8];
 #pragma unroll
@@ -528,19 +542,6 @@ __global__ void __launch_bounds__(VERIFY_THREADS) verify_kernel(const VerifyReco
 // with aligned 32-bit loads re-aligned and byte-swapped by one PRMT per word.  The buffer must be
 // readable 8 bytes past its end (the library pads its device copy).  Bound by the alu pipe like the
 // search kernels (about 1300 instructions per 64 bytes), not by HBM.
-__device__ __forceinline__ void compress_unrolled(uint32_t st[8], uint32_t (&w)[16]) {
-    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
-#pragma unroll
-    for (int t = 0; t < 64; t++) {
-        if (t >= 16)
-            w[t & 15] = w[t & 15] + small_sigma0(w[(t + 1) & 15]) + w[(t + 9) & 15] + small_sigma1(w[(t + 14) & 15]);
-        uint32_t t1 = h + big_sigma1(e) + ch(e, f, g) + (Kc(t) + w[t & 15]);
-        uint32_t t2 = big_sigma0(a) + maj(a, b, c);
-        h = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
-    }
-    st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
-}
-
 __global__ void __launch_bounds__(128) sha256_batch_kernel(const uint8_t* data, const unsigned long long* offsets,
                                                           uint32_t n, uint32_t* out) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
