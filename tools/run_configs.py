@@ -43,10 +43,11 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--difficulty9", type=float, nargs="+", default=[9.0, 9.3, 9.5])
     ap.add_argument("--templates", type=int, default=4096)
+    ap.add_argument("--skip4", action="store_true", help="config 5 only")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "configs.json"))
     a = ap.parse_args()
     out = {"gpus": a.gpus, "config4": [], "config5": None}
-    for d9 in a.difficulty9:
+    for d9 in ([] if a.skip4 else a.difficulty9):
         rule = T.DifficultyRule.derive(d9, PREV)
         prefix = t0_prefix(d9)
         n = 1

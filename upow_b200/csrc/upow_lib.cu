@@ -735,123 +735,6 @@ extern "C" int upow_sweep(upow_ctx* ctx, int slot, uint64_t nonce_lo, uint64_t n
     }
 }
 
-namespace {
-
-int ensure_batch_capacity(upow_ctx* ctx, Device& d, uint32_t n) {
-    if (n <= d.batch_cap) return UPOW_OK;
-    CU_TRY(ctx, cudaSetDevice(d.id));
-    cudaFree(d.d_jobs); cudaFree(d.d_active); cudaFree(d.d_best); cudaFree(d.d_bdigest);
-    d.d_jobs = nullptr; d.d_active = nullptr; d.d_best = nullptr; d.d_bdigest = nullptr;
-    d.batch_cap = 0;
-    CU_TRY(ctx, cudaMalloc(&d.d_jobs, sizeof(BatchJob) * n));
-    CU_TRY(ctx, cudaMalloc(&d.d_active, sizeof(uint32_t) * n));
-    CU_TRY(ctx, cudaMalloc(&d.d_best, sizeof(unsigned long long) * n));
-    CU_TRY(ctx, cudaMalloc(&d.d_bdigest, 32 * n));
-    d.batch_cap = n;
-    return UPOW_OK;
-}
-
-// All templates assigned to one device: rounds over growing nonce chunks until every
-// template has its minimum or the space is exhausted.
-//
-// "any" mode (first_round != nullptr): every device walks the SAME fixed sequence of rounds
-// (fixed_h_round H values each) and stops once it has completed the earliest round in which any
-// device found something; the caller then picks the lowest template index among the finds of that
-// round, which makes the answer independent of the number of GPUs and of timing.
-int run_batch_on_device(upow_ctx* ctx, Device& d, const std::vector<BatchJob>& jobs, uint64_t max_nonce,
-                        std::vector<unsigned long long>* best_out, std::vector<uint32_t>* digests_out,
-                        uint64_t* hashes, double* kernel_ms, uint32_t* launches,
-                        std::atomic<uint32_t>* first_round = nullptr, uint64_t fixed_h_round = 0) {
-    const uint32_t n = (uint32_t)jobs.size();
-    best_out->assign(n, ~0ull);
-    digests_out->assign((size_t)n * 8, 0);
-    if (n == 0) return UPOW_OK;
-    int rc = ensure_batch_capacity(ctx, d, n);
-    if (rc != UPOW_OK) return rc;
-    CU_TRY(ctx, cudaSetDevice(d.id));
-    CU_TRY(ctx, cudaMemcpyAsync(d.d_jobs, jobs.data(), sizeof(BatchJob) * n, cudaMemcpyHostToDevice, d.stream));
-    CU_TRY(ctx, cudaMemsetAsync(d.d_best, 0xff, sizeof(unsigned long long) * n, d.stream));
-    std::vector<uint32_t> active(n);
-    for (uint32_t i = 0; i < n; i++) active[i] = i;
-    std::vector<unsigned long long> best(n, ~0ull);
-    const uint32_t n_warps = d.batch_grid * 8;
-    const uint32_t h_total = (uint32_t)((max_nonce + 0xffff) >> 16);
-    // expected work per template from its rule: 16^n_target * 16/charset
-    uint32_t h_done = 0;
-    bool has_v1 = false, has_v2 = false;
-    for (auto& j : jobs) (j.tail.layout == LAYOUT_V1 ? has_v1 : has_v2) = true;
-    uint32_t round_no = 0;
-    while (!active.empty() && h_done < h_total) {
-        if (ctx->cancel.load(std::memory_order_relaxed)) return UPOW_CANCELLED;
-        if (first_round && round_no > first_round->load()) break;
-        // round size: enough H values that the launch holds >= 16 items per warp, and at least
-        // a quarter of the typical expected search length of the remaining templates
-        double expect = 0;
-        for (uint32_t idx : active) {
-            const Rule& r = jobs[idx].rule;
-            double e = 1;
-            for (uint32_t q = 0; q < std::min<uint32_t>(r.n_target, 16); q++) e *= 16;
-            expect = std::max(expect, e * 16.0 / r.charset_count);
-        }
-        uint64_t h_round = (uint64_t)(expect / 4 / 65536.0);
-        const uint64_t h_min = ((uint64_t)16 * n_warps + 2047) / 2048 / active.size() + 1;
-        h_round = std::max<uint64_t>(std::max<uint64_t>(h_round, h_min), 1);
-        if (first_round) h_round = fixed_h_round;
-        h_round = std::min<uint64_t>(h_round, h_total - h_done);
-        uint32_t hc = 64;
-        while (hc > 1 && hc > h_round) hc >>= 1;
-        BatchArgs a;
-        memset(&a, 0, sizeof a);
-        a.jobs = d.d_jobs; a.active = d.d_active; a.best = d.d_best; a.res = d.d_res;
-        a.nonce_hi = max_nonce;
-        a.n_active = (uint32_t)active.size();
-        a.h_lo = h_done; a.h_count = (uint32_t)h_round; a.hc = hc;
-        a.items_per_job = (uint32_t)((h_round + hc - 1) / hc) * 2048;
-        fill_opaque(&a.q);
-        DevResult init;
-        memset(&init, 0, sizeof init);
-        init.best = ~0ull;
-        *d.h_res = init;
-        CU_TRY(ctx, cudaMemcpyAsync(d.d_res, d.h_res, sizeof(DevResult), cudaMemcpyHostToDevice, d.stream));
-        CU_TRY(ctx, cudaMemcpyAsync(d.d_active, active.data(), sizeof(uint32_t) * active.size(), cudaMemcpyHostToDevice, d.stream));
-        CU_TRY(ctx, cudaEventRecord(d.ev0, d.stream));
-        if (has_v1) { batch_kernel<LAYOUT_V1><<<d.batch_grid, 256, 0, d.stream>>>(a); (*launches)++; }
-        if (has_v1 && has_v2)  // both launches walk the same item list: rewind the queue in between
-            CU_TRY(ctx, cudaMemsetAsync(&d.d_res->next_item, 0, sizeof(unsigned long long), d.stream));
-        if (has_v2) { batch_kernel<LAYOUT_V2><<<d.batch_grid, 256, 0, d.stream>>>(a); (*launches)++; }
-        CU_TRY(ctx, cudaGetLastError());
-        CU_TRY(ctx, cudaEventRecord(d.ev1, d.stream));
-        int st = wait_event(ctx, d, d.ev1, 0);
-        if (st < 0) return st;
-        CU_TRY(ctx, cudaMemcpyAsync(best.data(), d.d_best, sizeof(unsigned long long) * n, cudaMemcpyDeviceToHost, d.stream));
-        CU_TRY(ctx, cudaMemcpyAsync(d.h_res, d.d_res, sizeof(DevResult), cudaMemcpyDeviceToHost, d.stream));
-        CU_TRY(ctx, cudaStreamSynchronize(d.stream));
-        float ms = 0;
-        CU_TRY(ctx, cudaEventElapsedTime(&ms, d.ev0, d.ev1));
-        *kernel_ms += ms;
-        *hashes += d.h_res->items_done * 32ull * hc;
-        if (st == UPOW_CANCELLED) return UPOW_CANCELLED;
-        std::vector<uint32_t> still;
-        for (uint32_t idx : active)
-            if (best[idx] == ~0ull) still.push_back(idx);
-        if (first_round && still.size() != active.size()) {  // something was found in this round
-            uint32_t cur = first_round->load();
-            while (round_no < cur && !first_round->compare_exchange_weak(cur, round_no)) {}
-        }
-        active.swap(still);
-        h_done += (uint32_t)h_round;
-        round_no++;
-    }
-    batch_digest_kernel<<<(n + 127) / 128, 128, 0, d.stream>>>(d.d_jobs, d.d_best, n, d.d_bdigest);
-    CU_TRY(ctx, cudaGetLastError());
-    CU_TRY(ctx, cudaMemcpyAsync(digests_out->data(), d.d_bdigest, 32 * (size_t)n, cudaMemcpyDeviceToHost, d.stream));
-    CU_TRY(ctx, cudaStreamSynchronize(d.stream));
-    *best_out = best;
-    return UPOW_OK;
-}
-
-}  // namespace
-
 // Shared front half of upow_search_batch / upow_search_any: validate and prepare every template.
 namespace {
 int prepare_templates(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates, std::vector<Prepared>* prep,
@@ -887,6 +770,175 @@ int prepare_templates(upow_ctx* ctx, uint32_t n_templates, const upow_template* 
 }
 }  // namespace
 
+namespace {
+
+int ensure_batch_capacity(upow_ctx* ctx, Device& d, uint32_t n) {
+    if (n <= d.batch_cap) return UPOW_OK;
+    CU_TRY(ctx, cudaSetDevice(d.id));
+    cudaFree(d.d_jobs); cudaFree(d.d_active); cudaFree(d.d_best); cudaFree(d.d_bdigest);
+    d.d_jobs = nullptr; d.d_active = nullptr; d.d_best = nullptr; d.d_bdigest = nullptr;
+    d.batch_cap = 0;
+    CU_TRY(ctx, cudaMalloc(&d.d_jobs, sizeof(BatchJob) * n));
+    CU_TRY(ctx, cudaMalloc(&d.d_active, sizeof(uint32_t) * n));
+    CU_TRY(ctx, cudaMalloc(&d.d_best, sizeof(unsigned long long) * n));
+    CU_TRY(ctx, cudaMalloc(&d.d_bdigest, 32 * n));
+    d.batch_cap = n;
+    return UPOW_OK;
+}
+
+// expected hashes until a template's first valid nonce: 16^n_target * 16 / charset
+double expected_hashes(const Rule& r) {
+    double e = 1;
+    for (uint32_t q = 0; q < std::min<uint32_t>(r.n_target, 16); q++) e *= 16;
+    return e * 16.0 / r.charset_count;
+}
+
+// The batch engine behind upow_search_batch and upow_search_any.
+//
+// Every GPU holds the whole job table.  The search advances in ROUNDS: in round r every template that
+// has no valid nonce yet is searched over the next h_round H values (h_round * 2^16 nonces), and the
+// still-active templates are dealt out evenly over the GPUs again at the start of every round -- a
+// static template-to-GPU assignment leaves the unlucky GPU with several per cent more work (the search
+// lengths are geometric).  All launches of a round are issued from this thread and then awaited
+// together.  stop_at_first: return after the first round in which anything was found.
+// best[i] = minimum valid nonce of template i or ~0ull; digests (8 words per template) from device 0.
+int run_batch_rounds(upow_ctx* ctx, const std::vector<Prepared>& prep, uint64_t max_nonce, bool stop_at_first,
+                     std::vector<unsigned long long>* best_out, std::vector<uint32_t>* digests_out,
+                     upow_result* stats, uint32_t* first_round_out) {
+    const uint32_t n = (uint32_t)prep.size();
+    const int n_dev = (int)ctx->devs.size();
+    best_out->assign(n, ~0ull);
+    digests_out->assign((size_t)n * 8, 0);
+    if (first_round_out) *first_round_out = 0xffffffffu;
+    if (n == 0) return UPOW_OK;
+    std::vector<BatchJob> jobs(n);
+    bool has_v1 = false, has_v2 = false;
+    for (uint32_t i = 0; i < n; i++) {
+        jobs[i].tail = prep[i].tail;
+        jobs[i].rule = prep[i].rule;
+        (jobs[i].tail.layout == LAYOUT_V1 ? has_v1 : has_v2) = true;
+    }
+    for (auto& d : ctx->devs) {
+        int rc = ensure_batch_capacity(ctx, d, n);
+        if (rc != UPOW_OK) return rc;
+        CU_TRY(ctx, cudaSetDevice(d.id));
+        CU_TRY(ctx, cudaMemcpyAsync(d.d_jobs, jobs.data(), sizeof(BatchJob) * n, cudaMemcpyHostToDevice, d.stream));
+        CU_TRY(ctx, cudaMemsetAsync(d.d_best, 0xff, sizeof(unsigned long long) * n, d.stream));
+    }
+    std::vector<unsigned long long>& best = *best_out;
+    std::vector<uint32_t> active(n);
+    for (uint32_t i = 0; i < n; i++) active[i] = i;
+    std::vector<std::vector<unsigned long long>> dev_best(n_dev, std::vector<unsigned long long>(n));
+    std::vector<uint64_t> dev_hashes(n_dev, 0);
+    std::vector<double> dev_ms(n_dev, 0.0);
+    uint32_t launches = 0;
+    const uint32_t h_total = (uint32_t)((max_nonce + 0xffff) >> 16);
+    uint32_t h_done = 0, round_no = 0;
+    uint64_t fixed_round = 0;
+    if (stop_at_first) {
+        // first success over all templates ~ the easiest rule's expectation spread over n templates
+        double e_min = expected_hashes(jobs[0].rule);
+        for (auto& j : jobs) e_min = std::min(e_min, expected_hashes(j.rule));
+        fixed_round = (uint64_t)(e_min / 4 / 65536.0 / n);
+    }
+    while (!active.empty() && h_done < h_total) {
+        if (ctx->cancel.load(std::memory_order_relaxed)) return UPOW_CANCELLED;
+        // round size: about a quarter of the expected remaining search length, but never so small that a
+        // GPU gets fewer than 16 items per warp
+        uint64_t h_round = fixed_round;
+        if (!stop_at_first) {
+            double expect = 0;
+            for (uint32_t idx : active) expect = std::max(expect, expected_hashes(jobs[idx].rule));
+            h_round = (uint64_t)(expect / 4 / 65536.0);
+        }
+        const uint64_t per_dev = (active.size() + n_dev - 1) / n_dev;
+        const uint64_t h_min = ((uint64_t)16 * ctx->devs[0].batch_grid * 8 + 2047) / 2048 / per_dev + 1;
+        if (!stop_at_first || round_no == 0) h_round = std::max<uint64_t>(std::max<uint64_t>(h_round, h_min), 1);
+        if (stop_at_first) fixed_round = h_round;   // every round of an "any" search has the same size
+        h_round = std::min<uint64_t>(h_round, h_total - h_done);
+        uint32_t hc = 64;
+        while (hc > 1 && hc > h_round) hc >>= 1;
+        // deal the active templates out: device di takes active[cut[di] .. cut[di+1])
+        std::vector<size_t> cut(n_dev + 1);
+        for (int di = 0; di <= n_dev; di++) cut[di] = active.size() * di / n_dev;
+        for (int di = 0; di < n_dev; di++) {
+            Device& d = ctx->devs[di];
+            const size_t cnt = cut[di + 1] - cut[di];
+            if (cnt == 0) continue;
+            CU_TRY(ctx, cudaSetDevice(d.id));
+            BatchArgs a;
+            memset(&a, 0, sizeof a);
+            a.jobs = d.d_jobs; a.active = d.d_active; a.best = d.d_best; a.res = d.d_res;
+            a.nonce_hi = max_nonce;
+            a.n_active = (uint32_t)cnt;
+            a.h_lo = h_done; a.h_count = (uint32_t)h_round; a.hc = hc;
+            a.items_per_job = (uint32_t)((h_round + hc - 1) / hc) * 2048;
+            fill_opaque(&a.q);
+            DevResult init;
+            memset(&init, 0, sizeof init);
+            init.best = ~0ull;
+            *d.h_res = init;
+            CU_TRY(ctx, cudaMemcpyAsync(d.d_res, d.h_res, sizeof(DevResult), cudaMemcpyHostToDevice, d.stream));
+            CU_TRY(ctx, cudaMemcpyAsync(d.d_active, active.data() + cut[di], sizeof(uint32_t) * cnt, cudaMemcpyHostToDevice, d.stream));
+            CU_TRY(ctx, cudaEventRecord(d.ev0, d.stream));
+            if (has_v1) { batch_kernel<LAYOUT_V1><<<d.batch_grid, 256, 0, d.stream>>>(a); launches++; }
+            if (has_v1 && has_v2)  // both launches walk the same item list: rewind the queue in between
+                CU_TRY(ctx, cudaMemsetAsync(&d.d_res->next_item, 0, sizeof(unsigned long long), d.stream));
+            if (has_v2) { batch_kernel<LAYOUT_V2><<<d.batch_grid, 256, 0, d.stream>>>(a); launches++; }
+            CU_TRY(ctx, cudaGetLastError());
+            CU_TRY(ctx, cudaEventRecord(d.ev1, d.stream));
+            // (no device-to-host copy here: into pageable memory it would block this thread until the kernel
+            // has finished and serialise the GPUs; results are fetched in the wait loop below)
+        }
+        bool cancelled = false;
+        for (int di = 0; di < n_dev; di++) {
+            Device& d = ctx->devs[di];
+            if (cut[di + 1] == cut[di]) continue;
+            CU_TRY(ctx, cudaSetDevice(d.id));
+            int st = wait_event(ctx, d, d.ev1, 0);
+            if (st < 0) return st;
+            if (st == UPOW_CANCELLED) cancelled = true;
+            CU_TRY(ctx, cudaMemcpyAsync(dev_best[di].data(), d.d_best, sizeof(unsigned long long) * n, cudaMemcpyDeviceToHost, d.stream));
+            CU_TRY(ctx, cudaMemcpyAsync(d.h_res, d.d_res, sizeof(DevResult), cudaMemcpyDeviceToHost, d.stream));
+            CU_TRY(ctx, cudaStreamSynchronize(d.stream));
+            float ms = 0;
+            CU_TRY(ctx, cudaEventElapsedTime(&ms, d.ev0, d.ev1));
+            dev_ms[di] += ms;
+            dev_hashes[di] += d.h_res->items_done * 32ull * hc;
+            for (size_t k = cut[di]; k < cut[di + 1]; k++) best[active[k]] = dev_best[di][active[k]];
+        }
+        if (cancelled) return UPOW_CANCELLED;
+        std::vector<uint32_t> still;
+        for (uint32_t idx : active)
+            if (best[idx] == ~0ull) still.push_back(idx);
+        const bool found_any = still.size() != active.size();
+        active.swap(still);
+        h_done += (uint32_t)h_round;
+        if (found_any && first_round_out && *first_round_out == 0xffffffffu) *first_round_out = round_no;
+        round_no++;
+        if (stop_at_first && found_any) break;
+    }
+    // digests of all winners on device 0
+    Device& d0 = ctx->devs[0];
+    CU_TRY(ctx, cudaSetDevice(d0.id));
+    CU_TRY(ctx, cudaMemcpyAsync(d0.d_best, best.data(), sizeof(unsigned long long) * n, cudaMemcpyHostToDevice, d0.stream));
+    batch_digest_kernel<<<(n + 127) / 128, 128, 0, d0.stream>>>(d0.d_jobs, d0.d_best, n, d0.d_bdigest);
+    CU_TRY(ctx, cudaGetLastError());
+    CU_TRY(ctx, cudaMemcpyAsync(digests_out->data(), d0.d_bdigest, 32 * (size_t)n, cudaMemcpyDeviceToHost, d0.stream));
+    CU_TRY(ctx, cudaStreamSynchronize(d0.stream));
+    if (stats) {
+        for (int di = 0; di < n_dev; di++) {
+            stats->per_device_hashes[di] = dev_hashes[di];
+            stats->per_device_kernel_ms[di] = dev_ms[di];
+            stats->hashes_done += dev_hashes[di];
+            stats->kernel_ms = std::max(stats->kernel_ms, dev_ms[di]);
+        }
+        stats->launches = launches;
+    }
+    return UPOW_OK;
+}
+}  // namespace
+
 extern "C" int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates,
                                  uint64_t max_nonce, upow_batch_item* results, upow_result* stats) {
     if (!ctx || (n_templates && (!templates || !results))) return UPOW_E_ARG;
@@ -897,63 +949,38 @@ extern "C" int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow
         if (max_nonce > NONCE_SPACE) return UPOW_E_ARG;
         const double t_begin = now_s();
         ctx->cancel.store(0, std::memory_order_relaxed);
-        const int n_dev = (int)ctx->devs.size();
         std::vector<Prepared> prep;
         int prc = prepare_templates(ctx, n_templates, templates, &prep, "upow_search_batch");
         if (prc != UPOW_OK) return prc;
-        // round-robin sharding of templates over the GPUs
-        std::vector<std::vector<BatchJob>> jobs(n_dev);
-        std::vector<std::vector<uint32_t>> owner(n_dev);
-        for (uint32_t i = 0; i < n_templates; i++) {
-            BatchJob j;
-            j.tail = prep[i].tail;
-            j.rule = prep[i].rule;
-            jobs[i % n_dev].push_back(j);
-            owner[i % n_dev].push_back(i);
-        }
-        std::vector<std::vector<unsigned long long>> best(n_dev);
-        std::vector<std::vector<uint32_t>> dig(n_dev);
-        std::vector<int> rcs(n_dev, UPOW_OK);
-        std::vector<uint64_t> hashes(n_dev, 0);
-        std::vector<double> ms(n_dev, 0.0);
-        std::vector<uint32_t> launches(n_dev, 0);
-        auto worker = [&](int di) {
-            rcs[di] = run_batch_on_device(ctx, ctx->devs[di], jobs[di], max_nonce, &best[di], &dig[di], &hashes[di],
-                                          &ms[di], &launches[di]);
-            if (rcs[di] != UPOW_OK) return;
-            // results of this device's templates, each cross-checked with the host SHA-256
-            for (size_t k = 0; k < owner[di].size(); k++) {
-                const uint32_t i = owner[di][k];
+        std::vector<unsigned long long> best;
+        std::vector<uint32_t> dig;
+        int rc = run_batch_rounds(ctx, prep, max_nonce, false, &best, &dig, stats, nullptr);
+        if (rc != UPOW_OK) return rc;
+        // every result is cross-checked with the host SHA-256 (spread over a few host threads)
+        std::atomic<int> vrc{UPOW_OK};
+        auto fill = [&](uint32_t lo, uint32_t hi) {
+            for (uint32_t i = lo; i < hi; i++) {
                 memset(&results[i], 0, sizeof results[i]);
-                if (best[di][k] == ~0ull) continue;
+                if (best[i] == ~0ull) continue;
                 results[i].found = 1;
-                results[i].nonce = (uint32_t)best[di][k];
-                for (int w = 0; w < 8; w++) store_be32(results[i].digest + 4 * w, dig[di][k * 8 + w]);
+                results[i].nonce = (uint32_t)best[i];
+                for (int w = 0; w < 8; w++) store_be32(results[i].digest + 4 * w, dig[(size_t)i * 8 + w]);
                 if (!host_verify(prep[i], results[i].nonce, results[i].digest)) {
                     set_err(ctx, "batch result " + std::to_string(i) + " failed the host cross-check");
-                    rcs[di] = UPOW_E_INTERNAL;
-                    return;
+                    vrc = UPOW_E_INTERNAL;
                 }
             }
         };
-        if (n_dev == 1) worker(0);
+        const uint32_t n_thr = n_templates >= 1024 ? std::min<uint32_t>(8, std::max(1u, std::thread::hardware_concurrency())) : 1;
+        if (n_thr == 1) fill(0, n_templates);
         else {
             std::vector<std::thread> th;
-            for (int i = 0; i < n_dev; i++) th.emplace_back(worker, i);
+            for (uint32_t t = 0; t < n_thr; t++)
+                th.emplace_back(fill, (uint32_t)((uint64_t)n_templates * t / n_thr), (uint32_t)((uint64_t)n_templates * (t + 1) / n_thr));
             for (auto& t : th) t.join();
         }
-        for (int di = 0; di < n_dev; di++) {
-            if (rcs[di] != UPOW_OK) return rcs[di];
-            if (stats) {
-                stats->per_device_hashes[di] = hashes[di];
-                stats->per_device_kernel_ms[di] = ms[di];
-                stats->hashes_done += hashes[di];
-                stats->kernel_ms = std::max(stats->kernel_ms, ms[di]);
-                stats->launches += launches[di];
-            }
-        }
         if (stats) stats->elapsed_s = now_s() - t_begin;
-        return UPOW_OK;
+        return vrc.load();
     } catch (const std::exception& e) {
         set_err(ctx, std::string("exception: ") + e.what());
         return UPOW_E_INTERNAL;
@@ -962,7 +989,6 @@ extern "C" int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow
         return UPOW_E_INTERNAL;
     }
 }
-
 
 extern "C" int upow_search_any(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates, uint64_t max_nonce,
                                uint32_t* out_index, upow_batch_item* out_item, upow_result* stats) {
@@ -980,69 +1006,21 @@ extern "C" int upow_search_any(upow_ctx* ctx, uint32_t n_templates, const upow_t
         std::vector<Prepared> prep;
         int prc = prepare_templates(ctx, n_templates, templates, &prep, "upow_search_any");
         if (prc != UPOW_OK) return prc;
-        const int n_dev = (int)ctx->devs.size();
-        std::vector<std::vector<BatchJob>> jobs(n_dev);
-        std::vector<std::vector<uint32_t>> owner(n_dev);
-        double expect = 0;  // hashes until the FIRST success over all templates ~ the easiest rule's expectation
-        for (uint32_t i = 0; i < n_templates; i++) {
-            BatchJob j;
-            j.tail = prep[i].tail;
-            j.rule = prep[i].rule;
-            jobs[i % n_dev].push_back(j);
-            owner[i % n_dev].push_back(i);
-            double e = 1;
-            for (uint32_t q = 0; q < std::min<uint32_t>(j.rule.n_target, 16); q++) e *= 16;
-            e = e * 16.0 / j.rule.charset_count;
-            expect = (i == 0) ? e : std::min(expect, e);
-        }
-        // one round = every template advances by h_round H values; sized so that a round holds about a
-        // quarter of the expected work to the first success, and at least 16 items per warp per GPU
-        uint64_t h_round = (uint64_t)(expect / 4 / 65536.0 / n_templates);
-        const uint64_t per_dev = (n_templates + n_dev - 1) / n_dev;
-        const uint64_t h_min = ((uint64_t)16 * ctx->devs[0].batch_grid * 8 + 2047) / 2048 / per_dev + 1;
-        h_round = std::max<uint64_t>(std::max<uint64_t>(h_round, h_min), 1);
-        std::atomic<uint32_t> first_round{0xffffffffu};
-        std::vector<std::vector<unsigned long long>> best(n_dev);
-        std::vector<std::vector<uint32_t>> dig(n_dev);
-        std::vector<int> rcs(n_dev, UPOW_OK);
-        std::vector<uint64_t> hashes(n_dev, 0);
-        std::vector<double> ms(n_dev, 0.0);
-        std::vector<uint32_t> launches(n_dev, 0);
-        auto worker = [&](int di) {
-            rcs[di] = run_batch_on_device(ctx, ctx->devs[di], jobs[di], max_nonce, &best[di], &dig[di], &hashes[di],
-                                          &ms[di], &launches[di], &first_round, h_round);
-        };
-        if (n_dev == 1) worker(0);
-        else {
-            std::vector<std::thread> th;
-            for (int i = 0; i < n_dev; i++) th.emplace_back(worker, i);
-            for (auto& t : th) t.join();
-        }
-        for (int di = 0; di < n_dev; di++) {
-            if (rcs[di] != UPOW_OK) return rcs[di];
-            if (stats) {
-                stats->per_device_hashes[di] = hashes[di];
-                stats->per_device_kernel_ms[di] = ms[di];
-                stats->hashes_done += hashes[di];
-                stats->kernel_ms = std::max(stats->kernel_ms, ms[di]);
-                stats->launches += launches[di];
-            }
-        }
+        std::vector<unsigned long long> best;
+        std::vector<uint32_t> dig;
+        uint32_t first_round = 0xffffffffu;
+        int rc = run_batch_rounds(ctx, prep, max_nonce, true, &best, &dig, stats, &first_round);
         if (stats) stats->elapsed_s = now_s() - t_begin;
-        const uint32_t r = first_round.load();
-        if (r == 0xffffffffu) return UPOW_EXHAUSTED;
-        // finds of round r (and only those) are complete on every device: nonce < (r+1) * h_round * 2^16
-        const unsigned long long limit = std::min<unsigned long long>((unsigned long long)(r + 1) * h_round << 16, max_nonce);
+        if (rc != UPOW_OK) return rc;
+        // the search stopped after the first round with a find: every recorded minimum belongs to that round,
+        // and the round boundaries do not depend on the number of GPUs -- take the lowest template index
         uint32_t win = 0xffffffffu;
-        int win_dev = -1;
-        size_t win_k = 0;
-        for (int di = 0; di < n_dev; di++)
-            for (size_t k = 0; k < owner[di].size(); k++)
-                if (best[di][k] < limit && owner[di][k] < win) { win = owner[di][k]; win_dev = di; win_k = k; }
-        if (win_dev < 0) { set_err(ctx, "upow_search_any: inconsistent round bookkeeping"); return UPOW_E_INTERNAL; }
+        for (uint32_t i = 0; i < n_templates; i++)
+            if (best[i] != ~0ull) { win = i; break; }
+        if (win == 0xffffffffu) return UPOW_EXHAUSTED;
         out_item->found = 1;
-        out_item->nonce = (uint32_t)best[win_dev][win_k];
-        for (int w = 0; w < 8; w++) store_be32(out_item->digest + 4 * w, dig[win_dev][win_k * 8 + w]);
+        out_item->nonce = (uint32_t)best[win];
+        for (int w = 0; w < 8; w++) store_be32(out_item->digest + 4 * w, dig[(size_t)win * 8 + w]);
         if (!host_verify(prep[win], out_item->nonce, out_item->digest)) {
             set_err(ctx, "upow_search_any: result failed the host cross-check");
             return UPOW_E_INTERNAL;
@@ -1057,7 +1035,6 @@ extern "C" int upow_search_any(upow_ctx* ctx, uint32_t n_templates, const upow_t
         return UPOW_E_INTERNAL;
     }
 }
-
 
 namespace {
 static_assert(sizeof(upow_block) == sizeof(VerifyRecord), "upow_block and VerifyRecord must have one layout");
