@@ -567,6 +567,7 @@ extern "C" int upow_search_min(upow_ctx* ctx, int slot, uint64_t start_nonce, ui
         int final_status = 0;  // first non-zero status/error seen
         std::vector<uint64_t> dev_hashes(n_dev, 0);
         std::vector<double> dev_ms(n_dev, 0.0);
+        std::vector<uint64_t> dev_tile(n_dev, ~0ull);   // tile each device is working on (under mu)
         std::atomic<uint32_t> launches{0};
 
         auto worker = [&](int di) {
@@ -581,6 +582,7 @@ extern "C" int upow_search_min(upow_ctx* ctx, int slot, uint64_t start_nonce, ui
                     if (ctx->cancel.load(std::memory_order_relaxed)) { final_status = UPOW_CANCELLED; return; }
                     if (deadline > 0 && now_s() > deadline) { final_status = UPOW_EXHAUSTED; return; }
                     t = next_tile++;
+                    dev_tile[di] = t;
                 }
                 const uint64_t ts_idx = t / tiles_per_ts, k = t % tiles_per_ts;
                 if (ts_idx != cached_ts) {
@@ -607,7 +609,20 @@ extern "C" int upow_search_min(upow_ctx* ctx, int slot, uint64_t start_nonce, ui
                 dev_hashes[di] += o.hashes;
                 dev_ms[di] += o.kernel_ms;
                 if (di == 0 && o.sm_mhz > 0) result->sm_clock_mhz = o.sm_mhz;
-                if (o.found && t < found_tile) { found_tile = t; found_nonce = o.nonce; }
+                dev_tile[di] = ~0ull;
+                if (t > found_tile) continue;   // a tile behind an earlier find: stopped early on purpose, result unused
+                if (o.found && t < found_tile) {
+                    found_tile = t;
+                    found_nonce = o.nonce;
+                    // tiles after this one can no longer matter: stop the GPUs that are still working on them
+                    for (int oj = 0; oj < n_dev; oj++) {
+                        if (oj == di || dev_tile[oj] == ~0ull || dev_tile[oj] <= t) continue;
+                        Device& od = ctx->devs[oj];
+                        if (cudaSetDevice(od.id) == cudaSuccess)
+                            cudaMemcpyAsync(&od.d_res->abort_flag, od.h_one, sizeof(unsigned int), cudaMemcpyHostToDevice, od.ctrl);
+                    }
+                    cudaSetDevice(d.id);
+                }
                 // an aborted tile (cancel / deadline) may have skipped nonces: its "not found" is not final
                 if (o.status != 0 && final_status == 0) final_status = o.status;
             }
@@ -621,6 +636,10 @@ extern "C" int upow_search_min(upow_ctx* ctx, int slot, uint64_t start_nonce, ui
                 for (auto& t : th) t.join();
             }
         }
+        // abort words travel on the control streams: make sure none is still in flight when the next call
+        // resets the device-side result block
+        for (auto& d : ctx->devs)
+            if (cudaSetDevice(d.id) == cudaSuccess) cudaStreamSynchronize(d.ctrl);
         result->launches = launches.load();
         for (int i = 0; i < n_dev; i++) {
             result->per_device_hashes[i] = dev_hashes[i];
