@@ -341,3 +341,27 @@ def test_miner_main_round_structure_with_multiplier(monkeypatch, capsys):
     assert 1_699_999_990 < int.from_bytes(raw[-10:-6], "little") <= 1_700_000_000
     assert raw[96:128].hex() == O.calculate_merkle_root(body["txs"])
     assert "BLOCK MINED" in capsys.readouterr().out
+
+
+def test_null_arguments_are_rejected_without_a_gpu():
+    """Every entry point checks its pointers before touching CUDA: NULL context / outputs give UPOW_E_ARG (-1)."""
+    import upow_b200
+    from upow_b200 import _lib
+    L = upow_b200.load()
+    res, lim = _lib.Result(), _lib.Limits()
+    cnt = C.c_uint64(0)
+    idx = C.c_uint32(0)
+    item = _lib.BatchItem()
+    assert L.upow_search_min(None, 0, 0, 1, C.byref(lim), C.byref(res)) == -1
+    assert L.upow_sweep(None, 0, 0, 16, None, 0, C.byref(cnt), None) == -1
+    assert L.upow_set_template(None, 0, b"x" * 134, 134, bytes(32), 4, 16) == -1
+    assert L.upow_search_batch(None, 0, None, 0, None, None) == -1
+    assert L.upow_search_any(None, 0, None, 0, C.byref(idx), C.byref(item), None) == -1
+    assert L.upow_verify_blocks(None, 0, None, None, None, None) == -1
+    assert L.upow_sha256_batch(None, 0, None, None, None, None) == -1
+    assert L.upow_cancel(None) == -1 and L.upow_destroy(None) == -1 and L.upow_flush_l2(None) == -1
+    assert L.upow_device_count(None) == -1 and L.upow_get_variant(None) == -1 and L.upow_set_variant(None, 0) == -1
+    assert L.upow_init(99, None, C.byref(C.c_void_p())) == -1 and L.upow_init(1, None, None) == -1
+    assert L.upow_microbench(0, -1, 10, None) == -1
+    assert L.upow_sweep_noalloc(0, None, 134, bytes(32), 4, 16, 0, 16, None, 0, C.byref(cnt)) == -1
+    assert L.upow_variant_count() >= 9 and b"plain" in L.upow_variant_name(0) and L.upow_variant_name(999) == b""
