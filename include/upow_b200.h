@@ -71,6 +71,9 @@ typedef struct upow_device_info {
     int32_t max_sm_clock_khz;
     int32_t search_grid_blocks;   /* persistent grid used by the search kernels */
     uint64_t total_mem;
+    int32_t peer_devices;         /* how many of the context's other GPUs this one reaches by peer access (finds
+                                     travel GPU to GPU; without it the host relays them) */
+    int32_t reserved0;
 } upow_device_info;
 
 typedef struct upow_microbench_result {
@@ -165,6 +168,10 @@ int upow_search_any(upow_ctx* ctx, uint32_t n_templates, const upow_template* te
  * nor 108; out_digests (may be NULL) receives 32 bytes per block.  Blocks are split over the GPUs. */
 int upow_verify_blocks(upow_ctx* ctx, uint32_t n_blocks, const upow_block* blocks, uint8_t* out_valid,
                        uint8_t* out_digests, upow_result* stats);
+/* The same for records that already live in the memory of the context's GPU number device_index: all three
+ * pointers are DEVICE pointers there (d_digests may be NULL), nothing is copied. */
+int upow_verify_blocks_dev(upow_ctx* ctx, int device_index, uint32_t n_blocks, const upow_block* d_blocks,
+                           uint8_t* d_valid, uint8_t* d_digests, upow_result* stats);
 
 /* SHA-256 of n variable-length messages: message i is data[offsets[i] .. offsets[i+1]) (offsets has
  * n+1 entries, non-decreasing); out receives 32 bytes per message.  This is the per-transaction hashing
@@ -172,12 +179,17 @@ int upow_verify_blocks(upow_ctx* ctx, uint32_t n_blocks, const upow_block* block
  * (upow/upow_transactions/transaction.py:85-88) in one call.  Messages are split over the GPUs. */
 int upow_sha256_batch(upow_ctx* ctx, uint32_t n, const uint8_t* data, const uint64_t* offsets, uint8_t* out,
                       upow_result* stats);
+/* The same for data that already lives on the context's GPU number device_index: d_data, d_offsets and
+ * d_out are DEVICE pointers there; d_data must be 4-byte aligned and readable 8 bytes past offsets[n]. */
+int upow_sha256_batch_dev(upow_ctx* ctx, int device_index, uint32_t n, const uint8_t* d_data, const uint64_t* d_offsets,
+                          uint8_t* d_out, upow_result* stats);
 
 /* The library carries several builds of the search kernel that differ only in how the integer
  * work is spread over the SM's alu and fma issue pipes (DESIGN.md "pipe balance"); results are
  * identical.  Variant 0 is the plain-CUDA kernel.  The default is the fastest one measured on
  * B200; env UPOW_VARIANT overrides it at upow_init. */
 int upow_variant_count(void);
+int upow_default_variant(void);
 const char* upow_variant_name(int variant);
 int upow_get_variant(const upow_ctx* ctx);
 int upow_set_variant(upow_ctx* ctx, int variant);
@@ -204,8 +216,12 @@ int upow_sweep_noalloc(int device, const uint8_t* prefix, int prefix_len, const 
 const char* upow_noalloc_last_error(void);
 
 /* Stops a running search from another thread or a signal handler (only sets a flag; the
- * reference's equivalent is the parent terminating its workers, miner.py:155-156). */
+ * reference's equivalent is the parent terminating its workers, miner.py:155-156).  The flag is STICKY: a
+ * cancel that arrives while no search is running is not lost -- the next search / sweep / batch call on the
+ * context returns UPOW_CANCELLED at once.  The call that reports UPOW_CANCELLED consumes the flag;
+ * upow_clear_cancel drops a pending one (call it when a fresh template has been fetched). */
 int upow_cancel(upow_ctx* ctx);
+int upow_clear_cancel(upow_ctx* ctx);
 
 /* SHA-256 known-answer tests through the device code paths on `device`. 0 = all passed. */
 int upow_selftest(int device);

@@ -4,6 +4,8 @@ Run in the build container (needs /root/reference):
 
     python -m oracle.gen_golden            # mine_block / verifier vectors (about a minute)
     python -m oracle.gen_golden --sweep    # + the 2^32 sweep fixture (minutes, C oracle)
+    python -m oracle.gen_golden --cfg4     # only: minimality pin of BASELINE config 4 at difficulty 9.0 (C oracle, ~3e9 hashes)
+    python -m oracle.gen_golden --cfg5     # only: minimum nonce of all 4096 config-5 templates at 6.0 (C oracle, ~7e10 hashes)
 
 * ``mine_block_vectors.json``: every entry is ``miner.mine_block(start, inc, params)``
   (miner.py:30-114) run VERBATIM with only ``requests.post`` and ``timestamp()``
@@ -11,6 +13,11 @@ Run in the build container (needs /root/reference):
   (upow/manager.py:130-151) on the resulting block, also run verbatim.
 * ``verifier_vectors.json``: check_block_is_valid verdicts on near-miss blocks.
 * ``merkle_tree_vectors.json``: get_transactions_merkle_tree (upow/manager.py:365-378) on random blobs.
+* ``cfg4_t0v1_d9.json``: the first valid nonce of T0-v1 at difficulty 9.0 in the order of miner.py:86-89
+  (timestamp 1 700 000 000, nonces 0, 1, 2, ...), found by the C oracle walking every nonce below it.
+* ``cfg5_min_nonces.u32`` (+ ``.json``): the first valid nonce of each of the 4096 config-5 templates at
+  difficulty 6.0, one sequential C-oracle walk from nonce 0 per template.
+  Both are preceded by a check of the C oracle against the plain hashlib loop on 2^28 nonces.
 * ``sweep_t0v1_d5.u32`` (+ ``.json``): all valid nonces of the full 2^32 sweep of
   template T0-v1 at difficulty 5.0, enumerated by the C
   oracle (oracle/upow_oracle.c, full-message SHA-256 per nonce); the script refuses
@@ -25,6 +32,7 @@ import json
 import os
 import random
 import struct
+import time
 
 from . import c_oracle, ref_loader
 from . import upow_oracle as O
@@ -133,10 +141,98 @@ def sweep_fixture():
     print("sweep fixture:", len(nonces), fp)
 
 
+def _hashlib_slice(args):
+    prefix, difficulty, lo, hi = args
+    return O.all_valid_nonces(prefix, O.Rule(difficulty, O.T0_PREV_HASH), lo, hi)
+
+
+def check_c_oracle_against_hashlib(log, workers):
+    """SURVEY 8(c) tier T2: before the C oracle is trusted with sizes Python cannot reach, its valid-nonce set
+    over 2^28 nonces must equal the plain hashlib loop's (miner.py:51-61 restated in upow_oracle.py)."""
+    import multiprocessing as mp
+    prefix, d = O.t0_prefix(5.0), 5.0
+    n, parts = 1 << 28, 64
+    t0 = time.time()
+    with mp.get_context("fork").Pool(workers) as pool:
+        py = sum(pool.map(_hashlib_slice, [(prefix, d, n * i // parts, n * (i + 1) // parts) for i in range(parts)]), [])
+    t1 = time.time()
+    c, hashes = c_oracle.all_valid_nonces(prefix, O.Rule(d, O.T0_PREV_HASH), 0, n, threads=workers)
+    assert hashes == n and c == py, "C oracle disagrees with the hashlib loop"
+    log(f"C oracle == hashlib loop on [0, 2^28) of T0-v1 at 5.0: {len(py)} valid nonces "
+        f"(hashlib {t1 - t0:.0f} s, C {time.time() - t1:.0f} s, {workers} workers)")
+
+
+def cfg4_fixture(log, workers):
+    """BASELINE config 4 at difficulty 9.0: the first valid (timestamp, nonce) in the order of miner.py:86-89."""
+    d = 9.0
+    prefix, rule = O.t0_prefix(d), O.Rule(d, O.T0_PREV_HASH)
+    t0 = time.time()
+    nonce, hashes = c_oracle.min_valid_nonce(prefix, rule, 0, 1, 1 << 32, threads=workers)
+    assert nonce is not None, "no valid nonce at timestamp T0: rollover needed, extend this generator"
+    block = prefix + nonce.to_bytes(4, "little")
+    digest = hashlib.sha256(block).hexdigest()
+    assert rule.is_valid_block(block) and O.node_check_block_is_valid(block.hex(), d, {"hash": O.T0_PREV_HASH})
+    meta = {"template": "T0-v1", "difficulty": d, "timestamp": O.T0_TIMESTAMP, "rollovers": 0, "nonce": nonce,
+            "digest": digest, "hashes_walked": hashes,
+            "generator": "oracle/upow_oracle.c: every nonce below the answer hashed (full message) and rejected"}
+    with open(os.path.join(GOLDEN, "cfg4_t0v1_d9.json"), "w") as f:
+        json.dump(meta, f, indent=1)
+    log(f"cfg4 9.0: first valid nonce {nonce} digest {digest} after {hashes} hashes, {time.time() - t0:.0f} s")
+
+
+def _cfg5_one(i):
+    d = 6.0
+    n, hashes = c_oracle.min_valid_nonce(O.batch_template(i, d), O.Rule(d, O.T0_PREV_HASH), 0, 1, 1 << 32, threads=1)
+    return i, (-1 if n is None else n), hashes
+
+
+def cfg5_fixture(log, workers):
+    """BASELINE config 5: minimum valid nonce of each of the 4096 templates at difficulty 6.0."""
+    import multiprocessing as mp
+    t0 = time.time()
+    mins, total = [0] * 4096, 0
+    with mp.get_context("fork").Pool(workers) as pool:
+        for k, (i, n, hashes) in enumerate(pool.imap_unordered(_cfg5_one, range(4096), chunksize=4)):
+            assert n >= 0, f"template {i} has no valid nonce below 2^32"
+            mins[i] = n
+            total += hashes
+            if (k + 1) % 256 == 0:
+                log(f"cfg5: {k + 1}/4096 templates, {total} hashes, {time.time() - t0:.0f} s")
+    raw = struct.pack("<4096I", *mins)
+    fp = hashlib.sha256(raw).hexdigest()
+    with open(os.path.join(GOLDEN, "cfg5_min_nonces.u32"), "wb") as f:
+        f.write(raw)
+    meta = {"templates": "oracle.upow_oracle.batch_template(i, 6.0), i = 0..4095 (SURVEY 8(d) cfg 5)", "difficulty": 6.0,
+            "count": 4096, "sha256_u32le_in_template_order": fp, "sum_min_nonce_plus_1": sum(mins) + 4096,
+            "hashes_walked": total, "max_min_nonce": max(mins),
+            "generator": "oracle/upow_oracle.c, one sequential walk from nonce 0 per template (full-message SHA-256)"}
+    with open(os.path.join(GOLDEN, "cfg5_min_nonces.json"), "w") as f:
+        json.dump(meta, f, indent=1)
+    log(f"cfg5 fixture: fingerprint {fp}, {total} hashes, {time.time() - t0:.0f} s")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--sweep", action="store_true")
+    ap.add_argument("--cfg4", action="store_true")
+    ap.add_argument("--cfg5", action="store_true")
+    ap.add_argument("--workers", type=int, default=os.cpu_count() or 1)
     args = ap.parse_args()
+    if args.cfg4 or args.cfg5:
+        os.makedirs(GOLDEN, exist_ok=True)
+        logf = open(os.path.join(GOLDEN, "cfg_pins.log"), "a")
+
+        def log(msg):
+            line = time.strftime("%Y-%m-%dT%H:%M:%SZ ", time.gmtime()) + msg
+            print(line, flush=True)
+            logf.write(line + "\n")
+            logf.flush()
+        check_c_oracle_against_hashlib(log, args.workers)
+        if args.cfg4:
+            cfg4_fixture(log, args.workers)
+        if args.cfg5:
+            cfg5_fixture(log, args.workers)
+        return
     if not ref_loader.reference_available():
         raise SystemExit("reference tree not available; fixtures can only be generated in the build container")
     os.makedirs(GOLDEN, exist_ok=True)

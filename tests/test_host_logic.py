@@ -364,4 +364,8 @@ def test_null_arguments_are_rejected_without_a_gpu():
     assert L.upow_init(99, None, C.byref(C.c_void_p())) == -1 and L.upow_init(1, None, None) == -1
     assert L.upow_microbench(0, -1, 10, None) == -1
     assert L.upow_sweep_noalloc(0, None, 134, bytes(32), 4, 16, 0, 16, None, 0, C.byref(cnt)) == -1
-    assert L.upow_variant_count() >= 9 and b"plain" in L.upow_variant_name(0) and L.upow_variant_name(999) == b""
+    assert L.upow_variant_count() >= 2 and b"plain" in L.upow_variant_name(0) and L.upow_variant_name(999) == b""
+    assert 0 < L.upow_default_variant() < L.upow_variant_count()
+    assert L.upow_clear_cancel(None) == -1
+    assert L.upow_verify_blocks_dev(None, 0, 0, None, None, None, None) == -1
+    assert L.upow_sha256_batch_dev(None, 0, 0, None, None, None, None) == -1

@@ -25,8 +25,8 @@ out = {"generated_by": "tools/make_sass_counts.py (cuobjdump -sass of upow_b200/
        "bench_kernel": default, "kernels": kernels, "dram_bytes_per_launch": None}
 if default is None:
     # the default variant's v1 ENUM kernel = what bench.py times
-    # default variant 8 = Tune<ADD=1, SHR=0, RR=0, RQ=0, SR=0, SQ=0, CH=0, SHRQ=4>, 3 blocks/SM; layout 1, MODE_ENUM
-    cands = [k for k in kernels if "Tune<(int)1, (int)0, (int)0, (int)0, (int)0, (int)0, (int)0, (int)4>, (int)3, (int)256>" in k
+    # default variant = Tune<ADD=1, SHR=0, RR=0, RQ=0, SR=0, SQ=0, CH=0, SHRQ=4>, 3 blocks/SM; layout 1, MODE_ENUM
+    cands = [k for k in kernels if "Tune<(int)1, (int)0, (int)0, (int)0, (int)0, (int)0, (int)0, (int)4>, (int)3, (int)256" in k
              and "search_kernel_tuned<(int)1, (int)1," in k]
     out["bench_kernel"] = cands[0] if cands else None
 path = os.path.join(ROOT, "profiles", "sass_counts.json")

@@ -20,6 +20,7 @@ EXPORTS = [
     "upow_selftest", "upow_microbench_count", "upow_microbench", "upow_flush_l2", "upow_version",
     "upow_variant_count", "upow_variant_name", "upow_get_variant", "upow_set_variant",
     "upow_sweep_noalloc", "upow_noalloc_last_error", "upow_search_any", "upow_verify_blocks", "upow_sha256_batch",
+    "upow_clear_cancel", "upow_default_variant", "upow_verify_blocks_dev", "upow_sha256_batch_dev",
 ]
 NOALLOC_MAX_HITS = 65536
 
@@ -50,7 +51,7 @@ class Result(C.Structure):
 class DeviceInfo(C.Structure):
     _fields_ = [("name", C.c_char * 64), ("device_id", C.c_int32), ("sm_count", C.c_int32), ("cc_major", C.c_int32),
                 ("cc_minor", C.c_int32), ("max_sm_clock_khz", C.c_int32), ("search_grid_blocks", C.c_int32),
-                ("total_mem", C.c_uint64)]
+                ("total_mem", C.c_uint64), ("peer_devices", C.c_int32), ("reserved0", C.c_int32)]
 
 
 class MicrobenchResult(C.Structure):
@@ -110,7 +111,10 @@ def load():
                                   C.POINTER(BatchItem), C.POINTER(Result)]
     L.upow_verify_blocks.argtypes = [vp, C.c_uint32, C.POINTER(Block), C.c_char_p, C.c_char_p, C.POINTER(Result)]
     L.upow_sha256_batch.argtypes = [vp, C.c_uint32, C.c_char_p, u64p, C.c_char_p, C.POINTER(Result)]
+    L.upow_verify_blocks_dev.argtypes = [vp, C.c_int, C.c_uint32, vp, vp, vp, C.POINTER(Result)]
+    L.upow_sha256_batch_dev.argtypes = [vp, C.c_int, C.c_uint32, vp, vp, vp, C.POINTER(Result)]
     L.upow_cancel.argtypes = [vp]
+    L.upow_clear_cancel.argtypes = [vp]
     L.upow_selftest.argtypes = [C.c_int]
     L.upow_microbench_count.argtypes = []
     L.upow_microbench.argtypes = [C.c_int, C.c_int, C.c_uint32, C.POINTER(MicrobenchResult)]
@@ -279,7 +283,15 @@ class Context:
         return [out.raw[32 * i: 32 * i + 32] for i in range(n)], stats
 
     def cancel(self):
+        """Sticky: a cancel issued while nothing runs makes the NEXT search return UPOW_CANCELLED."""
         self._L.upow_cancel(self._h)
+
+    def clear_cancel(self):
+        self._L.upow_clear_cancel(self._h)
+
+    @property
+    def default_variant(self) -> int:
+        return self._L.upow_default_variant()
 
     @property
     def variant(self) -> int:

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libupow_b200.so")
 SOURCES = ["upow_lib.cu", "microbench.cu", "noalloc.cu"]
-HEADERS = ["kernels.cuh", "hot_loop.h", "sha256_core.h", "template_prep.h", os.path.join("..", "..", "include", "upow_b200.h")]
+HEADERS = ["kernels.cuh", "search_kernels.cuh", "hot_loop.h", "sha256_core.h", "template_prep.h", os.path.join("..", "..", "include", "upow_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-Xcompiler", "-fPIC,-O2,-Wall", "-shared", "-cudart", "static", "--threads", "3"]
 

@@ -7,10 +7,11 @@
 // streams, events or buffers is forbidden.  upow_init allocates result slots, a 16 MiB hit
 // buffer, pinned mirrors, streams and events per GPU; this entry point needs none of them.
 //
-// Its device-side scratch -- the work-queue / hit-count block and the buffer the kernel appends
-// valid nonces to -- lives in ONE file-scope static __device__ array of fixed size
-// (UPOW_NOALLOC_SCRATCH_BYTES, about 256 KiB).  Every GPU that loads the library carries that array
-// until the process exits, whether or not this entry point is ever called.
+// Its device-side scratch -- the work-queue / hit-count block, the stop word and the buffer the
+// kernel appends valid nonces to -- lives in ONE file-scope static __device__ array of fixed size
+// (UPOW_NOALLOC_SCRATCH_BYTES, about 256 KiB).  It belongs to the library's device code image: a GPU
+// holds it from the moment the CUDA runtime loads that image on it (with the default lazy loading,
+// at this entry point's first call on the device) until the process exits.
 //
 // Rules that follow from the design:
 //   * capacity is fixed: at most UPOW_NOALLOC_MAX_HITS nonces per call; a larger `cap` is refused;
@@ -18,10 +19,15 @@
 //     each call zeroes the control block before launching (the hit buffer needs no clearing: only
 //     entries below the final count are read);
 //   * two calls whose GPU work overlaps would trample each other's scratch.  Calls made through
-//     this entry point are serialised per device inside the process and run on the legacy
-//     default stream, synchronously; anything else that touches the array concurrently races;
-//   * the FIRST call on a device looks up the array's device address (cudaGetSymbolAddress) and
-//     uploads the SHA-256 round constants; make that first call before any stream capture begins.
+//     this entry point are serialised per device inside the process and each one waits for its own
+//     GPU work (on the calling thread's per-thread default stream, which needs no creation and does
+//     not synchronise with the host program's other streams); anything else that touches the array
+//     concurrently races;
+//   * every call looks up the array's device address (cudaGetSymbolAddress: a table lookup once the
+//     code image is loaded, and never stale after a device reset); the FIRST call on a device also
+//     sizes the grid and makes the runtime load the kernel and materialise the array, which takes
+//     device memory from the driver once: make that first call before the host program claims all
+//     free memory, and before any stream capture begins.
 //
 // In host code the array's name is only a handle, not a device pointer: the address handed to
 // the kernel is the one cudaGetSymbolAddress returns for the device that is current.
@@ -34,28 +40,17 @@
 #include <string>
 
 #include "../../include/upow_b200.h"
-#include "hot_loop.h"
-#include "sha256_core.h"
-#include "template_prep.h"
-
-// kernels.cuh also defines non-template kernels and a __constant__ table, and upow_lib.cu already
-// owns one copy of those symbols.  This file takes its own, separately named copy so that the
-// existing translation unit stays exactly as it is.
-namespace noalloc_tu {
-using namespace ::upow;
-#include "kernels.cuh"
-}  // namespace noalloc_tu
+#include "search_kernels.cuh"
 
 using namespace upow;
-using noalloc_tu::upow::DevResult;
-using noalloc_tu::upow::SearchArgs;
-using noalloc_tu::upow::search_kernel_tuned;
-using noalloc_tu::upow::MODE_ENUM;
 
 namespace {
 
-constexpr size_t CONTROL_BYTES = 256;  // DevResult lives here (64 B used), keeps the hit buffer 256-aligned
-static_assert(sizeof(DevResult) <= CONTROL_BYTES, "control block too small");
+// layout of the scratch: [0,128) DevResult, [128,136) kill word (never matches: nothing cancels this call),
+// [256, ...) hit buffer
+constexpr size_t CONTROL_BYTES = 256;
+constexpr size_t KILL_OFFSET = 128;
+static_assert(sizeof(DevResult) <= KILL_OFFSET, "control block too small");
 static_assert(UPOW_NOALLOC_SCRATCH_BYTES == CONTROL_BYTES + 4ull * UPOW_NOALLOC_MAX_HITS, "header and scratch disagree");
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[UPOW_NOALLOC_SCRATCH_BYTES];
@@ -63,9 +58,7 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[UPOW_NOALLOC_SC
 constexpr int MAX_DEVICES_SEEN = 64;
 struct PerDevice {
     std::mutex mu;
-    bool ready = false;
-    unsigned char* scratch = nullptr;  // device address of g_noalloc_scratch on this device
-    int grid = 0;
+    int grid = 0;                      // persistent grid (SMs x resident blocks), sized at the first call
 };
 PerDevice g_dev[MAX_DEVICES_SEEN];
 std::mutex g_err_mu;
@@ -87,22 +80,20 @@ void set_error(const std::string& s) {
         }                                                                                 \
     } while (0)
 
-// One-time set-up for the device that is current: device address of the scratch array, round
-// constants of this translation unit, persistent grid size.  Allocates nothing.
-int setup_current_device(PerDevice& pd) {
+// For the device that is current: device address of the scratch array (looked up on every call) and, once,
+// the persistent grid size.  Allocates nothing itself (the runtime loads the code image here if it has not yet).
+int resolve_current_device(PerDevice& pd, unsigned char** scratch) {
     void* p = nullptr;
     NA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));
-    uint32_t k[64];
-    for (int i = 0; i < 64; i++) k[i] = Kc(i);
-    NA_TRY(cudaMemcpyToSymbol(noalloc_tu::upow::K_DEV, k, sizeof k));
-    int dev = 0, sms = 0, per_sm = 0;
-    NA_TRY(cudaGetDevice(&dev));
-    NA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    NA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-        &per_sm, search_kernel_tuned<LAYOUT_V1, MODE_ENUM, NoAllocTune, 3>, 256, 0));
-    pd.scratch = static_cast<unsigned char*>(p);
-    pd.grid = sms * (per_sm < 1 ? 1 : per_sm);
-    pd.ready = true;
+    *scratch = static_cast<unsigned char*>(p);
+    if (pd.grid == 0) {
+        int dev = 0, sms = 0, per_sm = 0;
+        NA_TRY(cudaGetDevice(&dev));
+        NA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        NA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+            &per_sm, search_kernel_tuned<LAYOUT_V1, MODE_ENUM, NoAllocTune, 3>, 256, 0));
+        pd.grid = sms * (per_sm < 1 ? 1 : per_sm);
+    }
     return UPOW_OK;
 }
 
@@ -145,9 +136,12 @@ extern "C" int upow_sweep_noalloc(int device, const uint8_t* prefix, int prefix_
     std::lock_guard<std::mutex> lock(pd.mu);  // calls on one device never overlap inside this process
     int rc = UPOW_OK;
     do {
-        if (!pd.ready && (rc = setup_current_device(pd)) != UPOW_OK) break;
-        DevResult* res = reinterpret_cast<DevResult*>(pd.scratch);
-        uint32_t* hits = reinterpret_cast<uint32_t*>(pd.scratch + CONTROL_BYTES);
+        unsigned char* scratch = nullptr;
+        if ((rc = resolve_current_device(pd, &scratch)) != UPOW_OK) break;
+        DevResult* res = reinterpret_cast<DevResult*>(scratch);
+        unsigned long long* kill = reinterpret_cast<unsigned long long*>(scratch + KILL_OFFSET);
+        uint32_t* hits = reinterpret_cast<uint32_t*>(scratch + CONTROL_BYTES);
+        const cudaStream_t st = cudaStreamPerThread;
 
         SearchArgs a;
         memset(&a, 0, sizeof a);
@@ -157,33 +151,42 @@ extern "C" int upow_sweep_noalloc(int device, const uint8_t* prefix, int prefix_
         a.nonce_hi = nonce_hi;
         a.h_lo = (uint32_t)(nonce_lo >> 16);
         a.h_count = (uint32_t)((nonce_hi + 0xffff) >> 16) - a.h_lo;
+        a.lg_first = 0;
+        a.lg_step = 1;
+        a.lg_count = 2048;
         uint32_t hc = 64;
         while (hc > 1 && (uint64_t)((a.h_count + hc - 1) / hc) * 2048 < 4ull * pd.grid * 8) hc >>= 1;
         a.hc = hc;
         a.n_items = ((a.h_count + hc - 1) / hc) * 2048;
-        a.res = res;
-        a.out = hits;
-        a.cap = UPOW_NOALLOC_MAX_HITS;
+        a.sink.res = res;
+        a.sink.out = hits;
+        a.sink.cap = UPOW_NOALLOC_MAX_HITS;
+        a.sink.n_peers = 0;
+        a.kill.word = kill;
+        a.kill.serial = 1;
         fill_opaque(&a.q);
         if (tail.layout == LAYOUT_V2) prepare_v2_consts(tail, &a.v2);
 
         cudaError_t e;
-        // the control block still holds the previous call's counters: start from zero
-        if ((e = cudaMemsetAsync(res, 0, CONTROL_BYTES, 0)) != cudaSuccess) { rc = UPOW_E_CUDA; set_error(cudaGetErrorString(e)); break; }
+        // the control block still holds the previous call's counters: start from zero (a zero kill word means
+        // "serials 0..0", which the serial 1 of this launch never matches)
+        if ((e = cudaMemsetAsync(scratch, 0, CONTROL_BYTES, st)) != cudaSuccess) { rc = UPOW_E_CUDA; set_error(cudaGetErrorString(e)); break; }
         if (a.n_items) {
             if (tail.layout == LAYOUT_V1)
-                search_kernel_tuned<LAYOUT_V1, MODE_ENUM, NoAllocTune, 3><<<pd.grid, 256, 0, 0>>>(a);
+                search_kernel_tuned<LAYOUT_V1, MODE_ENUM, NoAllocTune, 3><<<pd.grid, 256, 0, st>>>(a);
             else
-                search_kernel_tuned<LAYOUT_V2, MODE_ENUM, NoAllocTune, 3><<<pd.grid, 256, 0, 0>>>(a);
+                search_kernel_tuned<LAYOUT_V2, MODE_ENUM, NoAllocTune, 3><<<pd.grid, 256, 0, st>>>(a);
             if ((e = cudaGetLastError()) != cudaSuccess) { rc = UPOW_E_CUDA; set_error(cudaGetErrorString(e)); break; }
         }
         DevResult host_res;
-        if ((e = cudaMemcpy(&host_res, res, sizeof host_res, cudaMemcpyDeviceToHost)) != cudaSuccess) {
+        if ((e = cudaMemcpyAsync(&host_res, res, sizeof host_res, cudaMemcpyDeviceToHost, st)) != cudaSuccess ||
+            (e = cudaStreamSynchronize(st)) != cudaSuccess) {
             rc = UPOW_E_CUDA; set_error(cudaGetErrorString(e)); break;
         }
         const uint64_t found = host_res.count;
         const uint64_t n_copy = std::min<uint64_t>(std::min<uint64_t>(found, UPOW_NOALLOC_MAX_HITS), cap);
-        if (n_copy && (e = cudaMemcpy(out_nonces, hits, n_copy * sizeof(uint32_t), cudaMemcpyDeviceToHost)) != cudaSuccess) {
+        if (n_copy && ((e = cudaMemcpyAsync(out_nonces, hits, n_copy * sizeof(uint32_t), cudaMemcpyDeviceToHost, st)) != cudaSuccess ||
+                       (e = cudaStreamSynchronize(st)) != cudaSuccess)) {
             rc = UPOW_E_CUDA; set_error(cudaGetErrorString(e)); break;
         }
         *out_count = found;
