@@ -39,10 +39,16 @@ typedef struct upow_ctx upow_ctx;
 /* Search limits.  Zero-initialise for the reference's behaviour (one pass over [start, 2^32)). */
 typedef struct upow_limits {
     uint64_t max_nonce;      /* exclusive end of the nonce space per timestamp; 0 means 2^32 */
-    uint32_t max_rollovers;  /* how many times "timestamp += 1, nonce = start" may be applied when the
+    uint32_t max_rollovers;  /* how many times "next timestamp, nonce = start" may be applied when the
                                 nonce space is exhausted (the reference instead dies with OverflowError
                                 and is restarted with a fresh timestamp, miner.py:87,149-156) */
-    uint32_t reserved0;
+    uint32_t rollover_backwards; /* 0: next timestamp = timestamp + 1 -- the order of the synthetic benchmark
+                                (SURVEY 8(d) cfg 4); blocks found that way carry a timestamp AHEAD of the wall
+                                clock and a node rejects them as "timestamp in the future" until the clock has
+                                caught up (upow/manager.py:456-460).  1: next timestamp = timestamp - 1, what a
+                                live miner needs: the node accepts last_block.timestamp < ts <= now
+                                (upow/manager.py:445-460), so start at now and allow at most
+                                now - last_block.timestamp - 1 rollovers */
     double time_limit_s;     /* <= 0: none.  The reference gives up after 90 s (miner.py:96-98) */
     uint64_t tile_nonces;    /* work granule handed to one GPU; 0 = library default */
 } upow_limits;
@@ -222,6 +228,11 @@ const char* upow_noalloc_last_error(void);
  * upow_clear_cancel drops a pending one (call it when a fresh template has been fetched). */
 int upow_cancel(upow_ctx* ctx);
 int upow_clear_cancel(upow_ctx* ctx);
+
+/* Hashes evaluated so far by the running (or the last) upow_search_min call, from any thread; it advances
+ * whenever a launch retires.  This is what the reference's progress line prints every 5 000 000 nonces
+ * (miner.py:89-95). */
+int upow_get_progress(const upow_ctx* ctx, uint64_t* hashes_done);
 
 /* SHA-256 known-answer tests through the device code paths on `device`. 0 = all passed. */
 int upow_selftest(int device);

@@ -32,6 +32,7 @@ from __future__ import annotations
 
 import hashlib
 import struct
+import time
 from decimal import Decimal
 from math import ceil, floor
 
@@ -173,6 +174,39 @@ def min_valid_nonce(prefix: bytes, rule: Rule, start_nonce: int = 0, nonce_incre
         if valid(sha(prefix + nonce.to_bytes(4, ENDIAN)).hexdigest()):
             return nonce
         nonce += nonce_increment
+    return None
+
+
+def miner_loop(prefix: bytes, rule: Rule, start_nonce: int = 0, nonce_increment: int = 1,
+               max_nonce: int = 1 << 32, progress=None):
+    """The hot loop with the SHAPE of miner.py:83-98, statement for statement: candidate = prefix + nonce LE32,
+    predicate on the hex digest (miner.py:51-56 / 60-61), then the increment and the per-iteration
+    `% check_interval` progress test (miner.py:89-95; the print goes to `progress` if given, the 90 s staleness
+    test is left to the caller).  Same answers as min_valid_nonce; this is the form bench.py times as the CPU arm,
+    because it pays every per-iteration cost the reference pays.  Returns None where the reference would raise
+    OverflowError (nonce >= 2**32) or when max_nonce is reached."""
+    sha = hashlib.sha256
+    target_prefix = rule.target_prefix
+    allowed_chars = rule.allowed_chars if rule.fractional > 0 else None
+    idiff = rule.int_difficulty
+    if allowed_chars is not None:
+        def is_valid_block(block_data: bytes) -> bool:
+            block_hash = sha(block_data).hexdigest()
+            return block_hash.startswith(target_prefix) and block_hash[idiff] in allowed_chars
+    else:
+        def is_valid_block(block_data: bytes) -> bool:
+            return sha(block_data).hexdigest().startswith(target_prefix)
+    nonce = start_nonce
+    check_interval = 5000000 * nonce_increment
+    t0 = time.time()
+    while nonce < max_nonce:
+        if is_valid_block(prefix + nonce.to_bytes(4, ENDIAN)):
+            return nonce
+        nonce += nonce_increment
+        if (nonce - start_nonce) % check_interval == 0:
+            elapsed = time.time() - t0
+            if progress is not None:
+                progress(nonce, elapsed)
     return None
 
 

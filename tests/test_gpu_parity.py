@@ -245,6 +245,75 @@ def test_two_queues_on_one_gpu_same_answer(sweep_fixture):
         assert (rc, res.nonce) == (0, want_n)
 
 
+def test_two_physical_gpus_same_answers(sweep_fixture):
+    """The same checks as test_two_queues_on_one_gpu_same_answer on two REAL devices (finds travel through peer
+    memory over NVLink); skipped on a one-GPU box."""
+    import upow_b200
+    try:
+        ctx2 = upow_b200.Context(device_ids=[0, 1])
+    except upow_b200.UpowError:
+        pytest.skip("needs two GPUs")
+    with ctx2:
+        prefix = bytes.fromhex(sweep_fixture["prefix"])
+        _set(ctx2, 0, prefix, make_rule(5.0, O.T0_PREV_HASH))
+        ns = sweep_fixture["nonces"]
+        for tile in (1 << 20, 0):
+            rc, res = ctx2.search_min(0, 0, 1, tile_nonces=tile)
+            assert (rc, res.nonce) == (0, 164867)
+            assert res.per_device_hashes[0] > 0 and res.per_device_hashes[1] > 0
+        got, stats = ctx2.sweep(0, 0, 1 << 30)
+        assert got == [n for n in ns if n < (1 << 30)]
+        _set(ctx2, 1, O.t0_prefix(6.3), make_rule(6.3, O.T0_PREV_HASH))
+        rc, res = ctx2.search_min(1)
+        assert (rc, res.nonce) == (0, 9436117)
+        d = 4.0
+        templates = [(O.batch_template(i, d), bytes.fromhex(O.T0_PREV_HASH), 4, 16) for i in range(64)]
+        items, _ = ctx2.search_batch(templates)
+        for i, (found, nonce, digest) in enumerate(items):
+            assert found and nonce == c_oracle.min_valid_nonce(templates[i][0], make_rule(d, O.T0_PREV_HASH))[0]
+        assert ctx2.device_info(0).peer_devices == 1
+
+
+def test_batch_on_two_queues_matches_one(gpu_ctx):
+    """The batch engine with two device slots on GPU 0: each takes half of every template's lgroups and the
+    finds reach the other slot's limit array; answers equal the single-queue run and the oracle."""
+    import upow_b200
+    d = 4.0
+    rule = make_rule(d, O.T0_PREV_HASH)
+    templates = [(O.batch_template(i, d) if i % 3 else O.t0_prefix(d, 2, O.T0_TIMESTAMP + i), bytes.fromhex(O.T0_PREV_HASH), 4, 16)
+                 for i in range(160)]
+    one, _ = gpu_ctx.search_batch(templates)
+    with upow_b200.Context(device_ids=[0, 0]) as ctx2:
+        two, stats = ctx2.search_batch(templates)
+        assert stats.per_device_hashes[0] > 0 and stats.per_device_hashes[1] > 0
+        rc, idx, nonce, digest, _ = ctx2.search_any(templates)
+    assert one == two
+    for i in range(0, 160, 9):
+        assert one[i][1] == c_oracle.min_valid_nonce(templates[i][0], rule)[0]
+    rc1, idx1, nonce1, digest1, _ = gpu_ctx.search_any(templates)
+    assert (rc, idx, nonce, digest) == (rc1, idx1, nonce1, digest1) and rc == 0
+
+
+@pytest.mark.parametrize("mix", ["v2", "mixed"])
+def test_batch_4096_templates_v2_and_mixed(gpu_ctx, mix):
+    """4096 templates of the 108-byte layout (and a mix of both layouts) at an oracle-checkable difficulty: the
+    batch kernel's hand-specialised 108-byte loop returns every template's minimum."""
+    d = 3.0
+    rule = make_rule(d, O.T0_PREV_HASH)
+    templates = []
+    for i in range(4096):
+        if mix == "v2" or i % 2:
+            prefix = O.t0_prefix(d, 2, O.T0_TIMESTAMP + i)
+        else:
+            prefix = O.batch_template(i, d)
+        templates.append((prefix, bytes.fromhex(O.T0_PREV_HASH), rule.int_difficulty, rule.charset_count))
+    items, stats = gpu_ctx.search_batch(templates)
+    for i, (found, nonce, digest) in enumerate(items):
+        want, _ = c_oracle.min_valid_nonce(templates[i][0], rule, threads=1)
+        assert found and nonce == want, (mix, i)
+        assert digest == O.digest_of(templates[i][0], want)
+
+
 def test_batch_templates_match_oracle(gpu_ctx):
     """config 5 shape at test size: per-template midstates, minimum nonce of each template."""
     d = 4.0
@@ -288,6 +357,72 @@ def test_time_limit_and_cancel(gpu_ctx):
     _set(gpu_ctx, 0, O.t0_prefix(4.0), make_rule(4.0, O.T0_PREV_HASH))
     rc, res = gpu_ctx.search_min(0)
     assert (rc, res.nonce) == (0, 62804)
+
+
+def test_cancel_before_search_start_is_honoured(gpu_ctx):
+    """The cancel flag is sticky: a cancel that lands between "template fetched" and "search started" (the
+    stale-work watcher runs in another thread) is not wiped by the next call -- that call returns CANCELLED at
+    once, and consumes the flag.  The reference's equivalent: the parent terminates its workers, miner.py:149-156."""
+    _set(gpu_ctx, 0, O.t0_prefix(16.0), make_rule(16.0, O.T0_PREV_HASH))
+    gpu_ctx.cancel()
+    t0 = time.time()
+    rc, res = gpu_ctx.search_min(0, max_rollovers=100000)
+    assert rc == 2 and res.hashes_done == 0 and time.time() - t0 < 0.5
+    # consumed: the next call runs
+    _set(gpu_ctx, 0, O.t0_prefix(4.0), make_rule(4.0, O.T0_PREV_HASH))
+    rc, res = gpu_ctx.search_min(0)
+    assert (rc, res.nonce) == (0, 62804)
+    # a pending cancel can be dropped explicitly (what miner.main does after fetching a fresh template)
+    gpu_ctx.cancel()
+    gpu_ctx.clear_cancel()
+    rc, res = gpu_ctx.search_min(0)
+    assert (rc, res.nonce) == (0, 62804)
+    # sweeps and batches honour a pending cancel too
+    gpu_ctx.cancel()
+    import upow_b200
+    buf_rc = gpu_ctx._L.upow_sweep(gpu_ctx._h, 0, 0, 1 << 20, None, 0, __import__("ctypes").byref(__import__("ctypes").c_uint64()), None)
+    assert buf_rc == upow_b200.UPOW_CANCELLED
+    rc, res = gpu_ctx.search_min(0)
+    assert (rc, res.nonce) == (0, 62804)
+
+
+def test_backwards_rollover_order(gpu_ctx):
+    """rollover_backwards: timestamps ts, ts-1, ts-2, ... (what a live miner needs: the node rejects timestamps
+    in the future, upow/manager.py:456-460).  First valid (rollover index, nonce) in that order."""
+    for version in (1, 2):
+        prefix = O.t0_prefix(3.0, version)
+        rule = make_rule(3.0, O.T0_PREV_HASH)
+        cap = max(O.min_valid_nonce(prefix, rule) // 3, 256)
+        want = None
+        for k in range(200):
+            n = O.min_valid_nonce(O.set_timestamp(prefix, O.T0_TIMESTAMP - k), rule, 0, 1, cap)
+            if n is not None:
+                want = (k, O.T0_TIMESTAMP - k, n)
+                break
+        assert want is not None and want[0] > 0
+        _set(gpu_ctx, 0, prefix, rule)
+        rc, res = gpu_ctx.search_min(0, max_nonce=cap, max_rollovers=200, rollover_backwards=True)
+        assert rc == 0 and (res.rollovers, res.timestamp, res.nonce) == want
+        assert bytes(res.digest) == O.digest_of(O.set_timestamp(prefix, want[1]), want[2])
+        rc, res = gpu_ctx.search_min(0, max_nonce=cap, max_rollovers=want[0] - 1, rollover_backwards=True)
+        assert rc == 1
+
+
+def test_progress_counter(gpu_ctx):
+    _set(gpu_ctx, 0, O.t0_prefix(16.0), make_rule(16.0, O.T0_PREV_HASH))
+    rc, res = gpu_ctx.search_min(0, max_nonce=1 << 28, max_rollovers=3)
+    assert rc == 1 and gpu_ctx.progress() == res.hashes_done == 4 << 28
+
+
+def test_hashes_done_tracks_the_answer(gpu_ctx):
+    """Early exit granularity: a search stops within a few H values of the find on every warp, so the hashes
+    evaluated stay close to nonce + 1 (BASELINE configs[1])."""
+    for d, want in ((6.3, 9436117), (5.0, 164867)):
+        _set(gpu_ctx, 0, O.t0_prefix(d), make_rule(d, O.T0_PREV_HASH))
+        rc, res = gpu_ctx.search_min(0)
+        assert (rc, res.nonce) == (0, want)
+        assert res.hashes_done >= want + 1 - 65536 * 32     # lanes of the last H values may not all have run
+        assert res.hashes_done <= 1.35 * (want + 1) + (1 << 22), (d, res.hashes_done)
 
 
 def test_argument_errors(gpu_ctx):

@@ -369,3 +369,107 @@ def test_null_arguments_are_rejected_without_a_gpu():
     assert L.upow_clear_cancel(None) == -1
     assert L.upow_verify_blocks_dev(None, 0, 0, None, None, None, None) == -1
     assert L.upow_sha256_batch_dev(None, 0, 0, None, None, None, None) == -1
+
+
+def test_miner_never_searches_an_exhausted_space_twice(monkeypatch, capsys):
+    """A B200 exhausts the 2^32 nonces of one timestamp in 0.23 s; the reference's restart-with-a-fresh-timestamp
+    (miner.py:87,149-156) would rebuild the SAME template inside the same second.  The mirror rolls the timestamp
+    backwards through the node's window (upow/manager.py:445-460) in one call and remembers what it exhausted."""
+    import types
+    from upow_b200 import miner, _lib
+
+    class ExhaustedCtx:
+        def __init__(self):
+            self.calls = []
+
+        def set_template(self, *a):
+            pass
+
+        def search_min(self, slot, start, stride, **kw):
+            self.calls.append(kw)
+            return _lib.UPOW_EXHAUSTED, _FakeResult(0, 0)
+
+    ctx = ExhaustedCtx()
+    miner.set_context(ctx)
+    miner._searched.clear()
+    monkeypatch.setitem(sys.modules, "requests", types.ModuleType("requests"))
+    monkeypatch.setattr(sys, "argv", ["miner.py", O.T0_ADDRESS_V1])
+    T = 1_700_000_000
+    params = {"difficulty": 9.0, "last_block": {"hash": O.T0_PREV_HASH, "id": 7, "timestamp": T - 20},
+              "pending_transactions_hashes": []}
+    monkeypatch.setattr(miner, "timestamp", lambda: T)
+    with pytest.raises(OverflowError):
+        miner.mine_block(0, 1, dict(params, last_block=dict(params["last_block"])))
+    # one call covered every acceptable timestamp: T, T-1, ..., T-19 (20 spaces), newest first
+    assert len(ctx.calls) == 1 and ctx.calls[0]["max_rollovers"] == 19 and ctx.calls[0]["rollover_backwards"] is True
+    with pytest.raises(OverflowError):      # same second again: nothing new to search, the GPU is not asked
+        miner.mine_block(0, 1, dict(params, last_block=dict(params["last_block"])))
+    assert len(ctx.calls) == 1
+    monkeypatch.setattr(miner, "timestamp", lambda: T + 3)
+    with pytest.raises(OverflowError):      # three new seconds: exactly those are searched
+        miner.mine_block(0, 1, dict(params, last_block=dict(params["last_block"])))
+    assert len(ctx.calls) == 2 and ctx.calls[1]["max_rollovers"] == 2
+    assert list(miner._searched.values()) == [(T + 3, T - 19)]
+    # a new chain tip is a new search space
+    params2 = dict(params, last_block={"hash": "cd" * 32, "id": 8, "timestamp": T + 2})
+    with pytest.raises(OverflowError):
+        miner.mine_block(0, 1, params2)
+    assert len(ctx.calls) == 3 and ctx.calls[2]["max_rollovers"] == 0      # only T+3 lies after the new tip's timestamp
+    miner.set_context(None)
+    miner._searched.clear()
+    capsys.readouterr()
+
+
+def test_miner_main_throttles_get_mining_info(monkeypatch, capsys):
+    """get_mining_info is rate limited to 30 a minute (upow/node/main.py:675-676): main() leaves at least
+    MINING_INFO_MIN_PERIOD_S between two requests even when every round ends at once."""
+    import types
+    from upow_b200 import miner, _lib
+
+    class Ctx:
+        cleared = 0
+
+        def set_template(self, *a):
+            pass
+
+        def search_min(self, *a, **k):
+            return _lib.UPOW_EXHAUSTED, _FakeResult(0, 0)
+
+        def clear_cancel(self):
+            Ctx.cleared += 1
+
+    clock = {"t": 1000.0}
+    sleeps, gets = [], []
+    monkeypatch.setattr(miner.time, "time", lambda: clock["t"])
+
+    def fake_sleep(s):
+        sleeps.append(s)
+        clock["t"] += s
+    monkeypatch.setattr(miner.time, "sleep", fake_sleep)
+
+    class Resp:
+        def json(self):
+            return {"ok": True, "result": {"difficulty": 9.0, "last_block": {"hash": O.T0_PREV_HASH, "id": 1, "timestamp": 1_699_999_999},
+                                           "pending_transactions_hashes": []}}
+
+    def fake_get(url, timeout=None):
+        gets.append(clock["t"])
+        if len(gets) > 4:
+            raise KeyboardInterrupt
+        return Resp()
+
+    fake = types.ModuleType("requests")
+    fake.get = fake_get
+    monkeypatch.setitem(sys.modules, "requests", fake)
+    monkeypatch.setattr(sys, "argv", ["miner.py", O.T0_ADDRESS_V1, "1"])
+    monkeypatch.setattr(miner, "timestamp", lambda: 1_700_000_000)
+    monkeypatch.delenv("UPOW_TEMPLATES", raising=False)
+    miner._searched.clear()
+    miner.set_context(Ctx())
+    with pytest.raises(KeyboardInterrupt):
+        miner.main()
+    miner.set_context(None)
+    miner._searched.clear()
+    assert all(b - a >= miner.MINING_INFO_MIN_PERIOD_S - 1e-9 for a, b in zip(gets, gets[1:]))
+    assert Ctx.cleared == 4          # every fresh template drops a cancel left over from the previous one
+    capsys.readouterr()

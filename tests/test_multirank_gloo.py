@@ -23,6 +23,18 @@ def test_partition_is_a_disjoint_cover_in_search_order():
         assert len(set(seen)) == len(seen)
 
 
+def test_lgroup_interleave_is_a_disjoint_cover():
+    """Inside one context: every nonce belongs to exactly one GPU's lgroup class, for any GPU count."""
+    for n in (1, 2, 3, 4, 5, 8):
+        classes = [set(sharding.lgroup_class(g, n)) for g in range(n)]
+        assert set().union(*classes) == set(range(sharding.LGROUPS))
+        assert sum(len(c) for c in classes) == sharding.LGROUPS
+        assert max(len(c) for c in classes) - min(len(c) for c in classes) <= 1
+        for nonce in (0, 31, 32, 65535, 164867, 4084426313, (1 << 32) - 1):
+            g = sharding.device_of_nonce(nonce, n)
+            assert ((nonce & 0xFFFF) >> 5) in classes[g]
+
+
 def test_split_range_alignment():
     for lo, hi, parts in ((0, 1 << 32, 8), (5, 1 << 30, 3), (12345, 7_000_001, 2), (0, 100, 4), (0, 0, 2)):
         shares = sharding.split_range(lo, hi, parts)
@@ -38,6 +50,7 @@ import os, sys, json
 sys.path.insert(0, {root!r})
 import torch, torch.distributed as dist
 from upow_b200 import sharding
+import bench
 dist.init_process_group("gloo")
 rank, world = dist.get_rank(), dist.get_world_size()
 mine = []
@@ -45,8 +58,8 @@ for step in range(3):
     mine += sharding.step_timestamps(step, rank, world, 1, 1000)
 gathered = [None] * world
 dist.all_gather_object(gathered, mine)
-elapsed = sharding.reduce_elapsed(1.0 + rank, dist)          # rank 1 is the slow one
-total = sharding.reduce_sum(float(len(mine)), dist)
+elapsed = bench.reduce_elapsed(1.0 + rank, dist)          # rank 1 is the slow one
+total = bench.reduce_sum(float(len(mine)), dist)
 if rank == 0:
     print(json.dumps({{"gathered": gathered, "elapsed": elapsed, "total": total}}))
 dist.destroy_process_group()

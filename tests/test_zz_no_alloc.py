@@ -17,19 +17,27 @@ def _t0(difficulty, version=1):
     return O.t0_prefix(difficulty, version), bytes.fromhex(O.T0_PREV_HASH), rule.int_difficulty, rule.charset_count
 
 
-def test_noalloc_matches_sweep_on_two_calls_in_a_row():
+def test_noalloc_matches_sweep_on_two_calls_in_a_row(sweep_fixture):
     import upow_b200
     from upow_b200 import _lib
+    from oracle import c_oracle
+    from oracle import upow_oracle as O
     with upow_b200.Context(1) as ctx:
         # call 1: many hits (difficulty 3.0, 2^24 nonces -> ~4096); call 2: few hits, other layout, other range
-        calls = [(_t0(3.0, 1), 0, 1 << 24), (_t0(4.5, 2), 1_000_003, 1_000_003 + (1 << 23)),
-                 (_t0(5.0, 1), 0, 1 << 28), (_t0(3.0, 1), 0, 1 << 24)]
-        for i, ((prefix, prev, n_int, cc), lo, hi) in enumerate(calls):
+        calls = [(_t0(3.0, 1), 3.0, 0, 1 << 24), (_t0(4.5, 2), 4.5, 1_000_003, 1_000_003 + (1 << 23)),
+                 (_t0(5.0, 1), 5.0, 0, 1 << 28), (_t0(3.0, 1), 3.0, 0, 1 << 24)]
+        for i, ((prefix, prev, n_int, cc), d, lo, hi) in enumerate(calls):
             ctx.set_template(0, prefix, prev, n_int, cc)
             want, _ = ctx.sweep(0, lo, hi)
             got = _lib.sweep_noalloc(0, prefix, prev, n_int, cc, lo, hi)
             assert got == want, f"call {i}"
             assert len(got) > 0
+            if i == 2:
+                # the reference's own answer for this call: the committed sweep fixture (hashlib fingerprint)
+                assert prefix.hex() == sweep_fixture["prefix"]
+                assert got == [n for n in sweep_fixture["nonces"] if n < (1 << 28)] and len(got) == 268
+            else:
+                assert got == c_oracle.all_valid_nonces(prefix, O.Rule(d, O.T0_PREV_HASH), lo, hi)[0], f"call {i} vs C oracle"
 
 
 def test_noalloc_edges_and_limits():

@@ -20,7 +20,7 @@ EXPORTS = [
     "upow_selftest", "upow_microbench_count", "upow_microbench", "upow_flush_l2", "upow_version",
     "upow_variant_count", "upow_variant_name", "upow_get_variant", "upow_set_variant",
     "upow_sweep_noalloc", "upow_noalloc_last_error", "upow_search_any", "upow_verify_blocks", "upow_sha256_batch",
-    "upow_clear_cancel", "upow_default_variant", "upow_verify_blocks_dev", "upow_sha256_batch_dev",
+    "upow_clear_cancel", "upow_get_progress", "upow_default_variant", "upow_verify_blocks_dev", "upow_sha256_batch_dev",
 ]
 NOALLOC_MAX_HITS = 65536
 
@@ -32,7 +32,7 @@ class UpowError(RuntimeError):
 
 
 class Limits(C.Structure):
-    _fields_ = [("max_nonce", C.c_uint64), ("max_rollovers", C.c_uint32), ("reserved0", C.c_uint32),
+    _fields_ = [("max_nonce", C.c_uint64), ("max_rollovers", C.c_uint32), ("rollover_backwards", C.c_uint32),
                 ("time_limit_s", C.c_double), ("tile_nonces", C.c_uint64)]
 
 
@@ -115,6 +115,7 @@ def load():
     L.upow_sha256_batch_dev.argtypes = [vp, C.c_int, C.c_uint32, vp, vp, vp, C.POINTER(Result)]
     L.upow_cancel.argtypes = [vp]
     L.upow_clear_cancel.argtypes = [vp]
+    L.upow_get_progress.argtypes = [vp, u64p]
     L.upow_selftest.argtypes = [C.c_int]
     L.upow_microbench_count.argtypes = []
     L.upow_microbench.argtypes = [C.c_int, C.c_int, C.c_uint32, C.POINTER(MicrobenchResult)]
@@ -188,9 +189,10 @@ class Context:
             raise UpowError(rc, "upow_set_template", self._err())
 
     def search_min(self, slot: int = 0, start_nonce: int = 0, stride: int = 1, max_nonce: int = 0,
-                   max_rollovers: int = 0, time_limit_s: float = 0.0, tile_nonces: int = 0):
+                   max_rollovers: int = 0, time_limit_s: float = 0.0, tile_nonces: int = 0,
+                   rollover_backwards: bool = False):
         """Returns (rc, Result); rc is UPOW_OK / UPOW_EXHAUSTED / UPOW_CANCELLED, errors raise."""
-        lim = Limits(max_nonce, max_rollovers, 0, time_limit_s, tile_nonces)
+        lim = Limits(max_nonce, max_rollovers, 1 if rollover_backwards else 0, time_limit_s, tile_nonces)
         res = Result()
         rc = self._L.upow_search_min(self._h, slot, start_nonce, stride, C.byref(lim), C.byref(res))
         if rc < 0:
@@ -288,6 +290,12 @@ class Context:
 
     def clear_cancel(self):
         self._L.upow_clear_cancel(self._h)
+
+    def progress(self) -> int:
+        """Hashes evaluated so far by the running (or last) search_min; callable from another thread."""
+        n = C.c_uint64(0)
+        self._L.upow_get_progress(self._h, C.byref(n))
+        return n.value
 
     @property
     def default_variant(self) -> int:

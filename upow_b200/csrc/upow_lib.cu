@@ -116,6 +116,7 @@ struct upow_ctx {
     std::vector<std::unique_ptr<Device>> devs;
     Slot slots[UPOW_MAX_SLOTS];
     std::atomic<int> cancel{0};   // sticky: stays set until a call consumes it or upow_clear_cancel
+    std::atomic<unsigned long long> progress{0};   // hashes of the running (or last) search, updated as launches retire
     std::mutex err_mu;
     std::string err;
     std::mutex api_mu;  // one search at a time per context
@@ -462,7 +463,7 @@ uint32_t pick_hc(uint32_t h_count, uint32_t lg_count, uint32_t n_warps) {
 // Arguments of a contiguous launch over nonces [lo, hi) of one (template, timestamp), restricted to the lgroup
 // class of device d (lg_first = its index, lg_step = number of devices sharing the range).
 void contiguous_args(upow_ctx* ctx, const Device& d, const Prepared& p, uint64_t lo, uint64_t hi, uint32_t lg_first,
-                     uint32_t lg_step, SearchArgs* a) {
+                     uint32_t lg_step, SearchArgs* a, uint32_t hc_cap = 64) {
     memset(a, 0, sizeof *a);
     a->tail = p.tail;
     a->rule = p.rule;
@@ -474,7 +475,7 @@ void contiguous_args(upow_ctx* ctx, const Device& d, const Prepared& p, uint64_t
     a->lg_step = lg_step;
     a->lg_count = lg_first < LGROUPS ? (LGROUPS - lg_first + lg_step - 1) / lg_step : 0;
     const uint32_t n_warps = d.variant_grid[ctx->variant] * (VARIANTS[ctx->variant].block / 32);
-    a->hc = pick_hc(a->h_count, a->lg_count, n_warps);
+    a->hc = std::min(pick_hc(a->h_count, a->lg_count, n_warps), std::max(hc_cap, 1u));
     a->n_items = ((a->h_count + a->hc - 1) / a->hc) * a->lg_count;
     a->kill.word = d.d_kill;
     fill_opaque(&a->q);
@@ -646,6 +647,11 @@ extern "C" int upow_cancel(upow_ctx* ctx) {
     ctx->cancel.store(1, std::memory_order_relaxed);
     return UPOW_OK;
 }
+extern "C" int upow_get_progress(const upow_ctx* ctx, uint64_t* hashes_done) {
+    if (!ctx || !hashes_done) return UPOW_E_ARG;
+    *hashes_done = ctx->progress.load(std::memory_order_relaxed);
+    return UPOW_OK;
+}
 extern "C" int upow_clear_cancel(upow_ctx* ctx) {
     if (!ctx) return UPOW_E_ARG;
     ctx->cancel.store(0, std::memory_order_relaxed);
@@ -670,8 +676,11 @@ int search_min_impl(upow_ctx* ctx, const Slot& s, uint64_t start_nonce, uint64_t
     const double t_begin = now_s();
     const double deadline = lim.time_limit_s > 0 ? t_begin + lim.time_limit_s : 0;
     const int n_dev = (int)ctx->devs.size();
+    ctx->progress.store(0, std::memory_order_relaxed);
     const bool contiguous = stride == 1;
     const bool tuned_strided = ctx->variant != 0;
+    // timestamp of rollover k: ts0 + k, or ts0 - k (mod 2^32 either way)
+    auto ts_add = [&](uint32_t k) { return lim.rollover_backwards ? 0u - k : k; };
 
     Prepared p0;
     if (!prepare_slot(s, 0, &p0)) return UPOW_E_INTERNAL;
@@ -699,6 +708,11 @@ int search_min_impl(upow_ctx* ctx, const Slot& s, uint64_t start_nonce, uint64_t
         first_granule = std::max<uint64_t>(first_granule, 1ull << 10);
         growth = 1;
     }
+    // The warp scheduler does not advance all warps evenly, so when a find is published some warps are still on
+    // early items while others have run ahead by a few items: short items keep that spread (work done beyond
+    // the answer) small where the whole search is short; long searches get the full 64-H items.
+    uint32_t hc_cap = 64;
+    while (hc_cap > 1 && (double)hc_cap * 32.0 > e_h) hc_cap >>= 1;
     uint32_t cur_ts = 0;
     uint64_t cur_pos = 0, cur_granule = first_granule;   // position inside the timestamp (nonces past start / steps)
     int rr_dev = 0;
@@ -750,7 +764,7 @@ int search_min_impl(upow_ctx* ctx, const Slot& s, uint64_t start_nonce, uint64_t
         std::lock_guard<std::mutex> lk(launch_mu);
         if (stop_status.load()) return 1;   // nothing is launched after the watchdog fired
         if (u.ts_idx != cached_ts) {
-            if (!prepare_slot(s, u.ts_idx, &p)) return UPOW_E_INTERNAL;
+            if (!prepare_slot(s, ts_add(u.ts_idx), &p)) return UPOW_E_INTERNAL;
             cached_ts = u.ts_idx;
         }
         u.launches.clear();
@@ -766,7 +780,7 @@ int search_min_impl(upow_ctx* ctx, const Slot& s, uint64_t start_nonce, uint64_t
             int rc;
             if (contiguous) {
                 SearchArgs a;
-                contiguous_args(ctx, d, p, u.lo, u.hi, (uint32_t)l.dev, (uint32_t)n_dev, &a);
+                contiguous_args(ctx, d, p, u.lo, u.hi, (uint32_t)l.dev, (uint32_t)n_dev, &a, hc_cap);
                 fill_sink(ctx, d, l, &u.launches, &a.sink, nullptr);
                 a.kill.serial = l.serial;
                 rc = enqueue_launch(ctx, d, l, [&](cudaStream_t st) { launch_search(d, a, MODE_MIN, ctx->variant, st); });
@@ -797,7 +811,11 @@ int search_min_impl(upow_ctx* ctx, const Slot& s, uint64_t start_nonce, uint64_t
     };
 
     for (;;) {
-        while (more && !found && rc_err == UPOW_OK && !stop_status.load() && launched - retired < window) {
+        // With growing units the first one covers four times the expected search length: it is launched alone
+        // (anything queued behind it would hash for nothing until the host has seen the find); after it,
+        // launches are pipelined.
+        const size_t depth = (growth > 1 && retired == 0) ? 1 : window;
+        while (more && !found && rc_err == UPOW_OK && !stop_status.load() && launched - retired < depth) {
             Unit& u = ring[launched % window];
             if (!next_unit(&u)) { more = false; break; }
             int rc = launch_unit(u);
@@ -817,6 +835,7 @@ int search_min_impl(upow_ctx* ctx, const Slot& s, uint64_t start_nonce, uint64_t
             if (rc != UPOW_OK) { if (rc_err == UPOW_OK) rc_err = rc; continue; }
             last_slot[l.dev] = l.slot;
             result->per_device_hashes[l.dev] += o.res.h_steps * 32ull;
+            ctx->progress.fetch_add(o.res.h_steps * 32ull, std::memory_order_relaxed);
             if (l.dev == 0 && o.sm_mhz > 0) result->sm_clock_mhz = o.sm_mhz;
             if (!found && o.res.best != NO_NONCE && (!unit_found || (uint32_t)o.res.best < unit_nonce)) {
                 unit_found = true;
@@ -858,7 +877,7 @@ int search_min_impl(upow_ctx* ctx, const Slot& s, uint64_t start_nonce, uint64_t
     if (rc_err != UPOW_OK) rc = rc_err;
     else if (found) {
         Prepared pf;
-        prepare_slot(s, found_ts, &pf);
+        prepare_slot(s, ts_add(found_ts), &pf);
         for (int i = 0; i < 8; i++) store_be32(result->digest + 4 * i, found_digest[i]);
         if (!host_verify(pf, found_nonce, result->digest)) {
             set_err(ctx, "device result failed the host SHA-256 / rule cross-check");
@@ -1154,7 +1173,7 @@ int run_batch(upow_ctx* ctx, const std::vector<Prepared>& prep, uint64_t max_non
                 uint64_t hr = (uint64_t)base << std::min<uint32_t>(ri / 8, 12);
                 hr = std::min<uint64_t>(std::min<uint64_t>(hr, 4096), h_total - h_done);
                 r.h_lo = h_done; r.h_count = (uint32_t)hr;
-                r.hc = (uint32_t)std::min<uint64_t>(64, std::max<uint64_t>(1, hr / 4));
+                r.hc = (uint32_t)std::min<uint64_t>(64, hr);   // one item per (template, lgroup) and round, up to 64 H
                 rounds.push_back(r);
                 for (auto& dp : ctx->devs) {
                     Device& d = *dp;

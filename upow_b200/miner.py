@@ -10,6 +10,15 @@ Kept from the reference (file:line are into /root/reference/miner.py):
 Replaced: only the loop at :83-98, by one ``upow_search_min`` call into libupow_b200.so.
 ``workers`` now means "number of GPUs driven by this one process" (env UPOW_GPUS overrides).
 
+Where a B200 forces a difference: the reference never exhausts a nonce space (2^32 hashes take it more than an
+hour), a B200 does so in 0.23 s.  The reference's answer to exhaustion is to die with OverflowError (:87) and be
+restarted with a fresh ``timestamp()`` (:149-156) -- which, inside the same wall-clock second, is the SAME
+template.  So here the search rolls the block timestamp BACKWARDS (now, now-1, ... down to
+last_block.timestamp+1: every one of those is acceptable to the node, upow/manager.py:445-460, none lies in
+the future) inside one library call, the spaces already searched for a chain tip are remembered and never
+searched again, and ``get_mining_info`` (rate limited to 30/minute, upow/node/main.py:675-676) is asked at most
+once every two seconds.
+
 There is no CPU fallback: without the CUDA library / a GPU this module raises.
 """
 from __future__ import annotations
@@ -28,8 +37,13 @@ __all__ = ["calculate_merkle_root", "mine_block", "mining_worker", "timestamp", 
 DEFAULT_NODE_URL = "http://localhost:3006/"
 STALE_AFTER_S = 90      # miner.py:96-98
 ROUND_LIMIT_S = 100     # miner.py:149-156
+MINING_INFO_MIN_PERIOD_S = 2.0   # 30 requests/minute at the node (upow/node/main.py:675-676)
+PROGRESS_PERIOD_S = 5.0          # a reference worker prints its rate every 5e6 hashes ~ 5 s (miner.py:89-95)
 
 _context = None
+# (prev_hash, wallet, merkle_root, difficulty, start, stride) -> (newest, oldest) timestamp whose nonce space
+# has been searched to the end without a find
+_searched: dict = {}
 
 
 def _node_url() -> str:
@@ -88,15 +102,36 @@ def mine_block(start_nonce: int = 0, nonce_increment: int = 1, mining_params: di
         print(f"Confirming {len(tx_hashes)} transactions")
     prefix = build_block_prefix(last_block["hash"], wallet_bytes, merkle_root, now, difficulty)
 
+    # which timestamps are still worth searching for this template: now, now-1, ... down to the block after the
+    # previous one, minus what earlier calls already searched to the end
+    key = (last_block["hash"], miner_wallet, merkle_root, str(difficulty), start_nonce, nonce_increment)
+    last_ts = last_block.get("timestamp", 0)
+    oldest = max(last_ts + 1 if isinstance(last_ts, int) else 0, now - int(os.environ.get("UPOW_MAX_ROLLOVERS", "3600")))
+    done = _searched.get(key)
+    if done is not None and done[1] <= now <= done[0]:
+        # this second was searched already: nothing new until the wall clock moves (the reference would hash
+        # the same 2^32 candidates again)
+        raise OverflowError("int too big to convert")
+    if done is not None and done[0] < now:
+        oldest = max(oldest, done[0] + 1)
+    max_rollovers = max(now - oldest, 0)
+
     ctx = get_context()
     ctx.set_template(0, prefix, rule.prev_hash, rule.n_int, rule.charset_count)
-    max_rollovers = int(os.environ.get("UPOW_MAX_ROLLOVERS", "0"))
-    rc, res = ctx.search_min(0, start_nonce, nonce_increment, time_limit_s=STALE_AFTER_S,
-                             max_rollovers=max_rollovers)
+    with _ProgressLines(ctx, start_nonce, started):
+        rc, res = ctx.search_min(0, start_nonce, nonce_increment, time_limit_s=STALE_AFTER_S,
+                                 max_rollovers=max_rollovers, rollover_backwards=True)
     elapsed = max(time.time() - started, 1e-9)
     print(f"Worker {start_nonce + 1}: " + str(int(res.hashes_done / elapsed / 1000)) + "k hash/s")
     if rc == _lib.UPOW_EXHAUSTED and elapsed <= STALE_AFTER_S:
-        # the reference dies here: nonce.to_bytes(4, ...) at 2**32 (miner.py:87)
+        # every timestamp of the window is exhausted.  The reference dies here: nonce.to_bytes(4, ...) at 2**32
+        # (miner.py:87)
+        lo_new = now - max_rollovers
+        if done is not None and done[0] + 1 >= lo_new:
+            lo_new = min(lo_new, done[1])      # joins the stretch searched earlier
+        _searched[key] = (now, lo_new)
+        if len(_searched) > 64:
+            _searched.pop(next(iter(_searched)))
         raise OverflowError("int too big to convert")
     if rc != _lib.UPOW_OK:
         return None  # stale or cancelled: nothing is submitted (miner.py:96-98)
@@ -104,6 +139,31 @@ def mine_block(start_nonce: int = 0, nonce_increment: int = 1, mining_params: di
     candidate = with_timestamp(prefix, res.timestamp) + res.nonce.to_bytes(4, ENDIAN)
     _submit(requests, candidate.hex(), tx_hashes, last_block["id"] + 1)
     exit()
+
+
+class _ProgressLines:
+    """While a search runs: the reference's "Worker N: <rate>k hash/s" line (miner.py:89-95) every few seconds.
+    (The reference prints it every 5e6 hashes, which is every ~5 s on a CPU core and 3800 times a second here.)"""
+
+    def __init__(self, ctx, start_nonce: int, started: float):
+        import threading
+        self.ctx, self.start_nonce, self.started = ctx, start_nonce, started
+        self._stop = threading.Event()
+        self._t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.wait(PROGRESS_PERIOD_S):
+            elapsed = max(time.time() - self.started, 1e-9)
+            hashes = self.ctx.progress() if hasattr(self.ctx, "progress") else 0
+            print(f"Worker {self.start_nonce + 1}: " + str(int(hashes / elapsed / 1000)) + "k hash/s")
+
+    def __enter__(self):
+        self._t.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        self._t.join(timeout=1)
 
 
 def _submit(requests, block_content_hex: str, tx_hashes, block_no: int):
@@ -132,22 +192,35 @@ def main():
 
     n_gpus = int(os.environ.get("UPOW_GPUS", sys.argv[2] if len(sys.argv) >= 3 else 1))
     get_context(n_gpus)
+    last_fetch = 0.0
     while True:
         print(f"Starting {n_gpus} workers")
         info = None
         while info is None:
+            wait = MINING_INFO_MIN_PERIOD_S - (time.time() - last_fetch)
+            if wait > 0:
+                time.sleep(wait)    # the node answers 429 above 30 requests a minute
+            last_fetch = time.time()
             try:
                 info = requests.get(_node_url() + "get_mining_info", timeout=5).json()["result"]
             except Exception as e:  # the reference retries forever, once a second
                 print(e)
                 time.sleep(1)
-        # optional extras beyond the reference (both off by default so the CLI behaves like miner.py):
+        if hasattr(get_context(), "clear_cancel"):
+            get_context().clear_cancel()   # a cancel raised for the PREVIOUS template must not stop this one
+        # optional extras beyond the reference (all off by default so the CLI behaves like miner.py):
         #   UPOW_TEMPLATES=N     race N templates of this reply (timestamps x transaction subsets), multiplier.py
-        #   UPOW_STALE_POLL_S=s  abandon the search as soon as the node's tip moves, stale.py
+        #   UPOW_STALE_POLL_S=s  abandon the search as soon as the node's tip moves (HTTP poll), stale.py
+        #   UPOW_STALE_WS=url    the same through the node's /ws "block" channel, e.g. ws://localhost:3006/ws
         n_templates = int(os.environ.get("UPOW_TEMPLATES", "1"))
         poll_s = float(os.environ.get("UPOW_STALE_POLL_S", "0"))
+        ws_url = os.environ.get("UPOW_STALE_WS", "")
         watcher = None
-        if poll_s > 0:
+        if ws_url:
+            from . import stale
+            watcher = stale.WebsocketWatcher(get_context(), ws_url)
+            watcher.__enter__()
+        elif poll_s > 0:
             from . import stale
             watcher = stale.StaleWatcher(get_context(), info["last_block"].get("id", 0),
                                          stale.http_tip_fetcher(_node_url()), poll_s)

@@ -3,8 +3,9 @@
 The reference shards by residue class over OS processes with no communication
 (miner.py:139-148).  Here the unit handed to one GPU is a whole nonce space of one timestamp
 (or a contiguous tile of it); units are numbered in the search order "timestamp, then nonce", and
-unit u of a step belongs to rank u // n_local, local GPU u % n_local.  No data-path collective:
-ranks only meet in a barrier and a max-reduce of the elapsed time.
+unit u of a step belongs to rank u // n_local, local GPU u % n_local (the independent-ranks leg of bench.py).
+Inside ONE library context the GPUs instead share every nonce space by lgroup interleave (lgroup_class below).
+No data-path collective either way: ranks only meet in a barrier and a max-reduce of the elapsed time (bench.py).
 """
 from __future__ import annotations
 
@@ -32,22 +33,15 @@ def split_range(lo: int, hi: int, parts: int, align: int = 1 << 16):
     return [(cuts[i], cuts[i + 1]) for i in range(parts)]
 
 
-def reduce_elapsed(elapsed_local: float, dist=None) -> float:
-    """Max over ranks of the elapsed time (the number the throughput is computed from)."""
-    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
-        return elapsed_local
-    import torch
-    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
-    t = torch.tensor([elapsed_local], dtype=torch.float64, device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+LGROUPS = 2048   # a nonce is (H << 16) | L; an lgroup is 32 consecutive L values, the unit a warp owns per H
 
 
-def reduce_sum(x: float, dist=None) -> float:
-    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
-        return x
-    import torch
-    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
-    t = torch.tensor([x], dtype=torch.float64, device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.SUM)
-    return float(t.item())
+def lgroup_class(device_index: int, n_devices: int):
+    """How ONE nonce space is shared by the GPUs of a context: device g searches the lgroups g, g + n, g + 2n, ...
+    of every H, i.e. the nonces whose bits 5..15 are congruent to g mod n (upow_lib.cu contiguous_args).  All GPUs
+    then walk H together and the lowest valid nonce is the minimum of the per-GPU minima."""
+    return range(device_index, LGROUPS, n_devices)
+
+
+def device_of_nonce(nonce: int, n_devices: int) -> int:
+    return ((nonce & 0xFFFF) >> 5) % n_devices

@@ -6,7 +6,8 @@ current tip -- by polling GET get_mining_info (rate limited to 30/minute, upow/n
 default 2.5 s period) or through the node's /ws "block" channel (subscribe_block -> "new_block" messages,
 websocket/socket_handlers.py:93-117, websocket/socket_utils.py:17-43) when aiohttp is importable -- and calls
 upow_cancel as soon as the block being built on is no longer the last one.  upow_search_min then returns
-UPOW_CANCELLED and the miner fetches a fresh template.
+UPOW_CANCELLED and the miner fetches a fresh template.  The cancel flag is sticky (include/upow_b200.h): a watcher
+that fires BEFORE the search has started still stops it; miner.main clears the flag when it has a fresh template.
 """
 from __future__ import annotations
 
@@ -79,3 +80,29 @@ def websocket_block_listener(ctx, ws_url: str, stop: threading.Event):
         return False
 
     return asyncio.run(listen())
+
+
+class WebsocketWatcher:
+    """Runs websocket_block_listener in a thread for the lifetime of one search (context manager)."""
+
+    def __init__(self, ctx, ws_url: str):
+        self.ctx, self.ws_url = ctx, ws_url
+        self.fired = False
+        self._stop = threading.Event()
+        self._thread: Optional[threading.Thread] = None
+
+    def _run(self):
+        try:
+            self.fired = bool(websocket_block_listener(self.ctx, self.ws_url, self._stop))
+        except Exception:
+            self.fired = False       # no websocket: the search simply runs to its own time limit
+
+    def __enter__(self):
+        self._thread = threading.Thread(target=self._run, daemon=True)
+        self._thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._thread:
+            self._thread.join(timeout=5)
