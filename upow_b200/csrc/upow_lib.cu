@@ -510,7 +510,11 @@ int finish_status(upow_ctx* ctx, int rc) {
 // ------------------------------------------------------------------------------------------
 // C-ABI
 // ------------------------------------------------------------------------------------------
+#ifdef UPOW_CHECKED
+extern "C" const char* upow_version(void) { return "upow_b200 0.2 (sm_100a, checked build: device-side index asserts)"; }
+#else
 extern "C" const char* upow_version(void) { return "upow_b200 0.2 (sm_100a)"; }
+#endif
 
 extern "C" const char* upow_last_error(const upow_ctx* ctx) {
     // a per-thread copy: the string inside the context may be rewritten by another thread at any time
@@ -1154,6 +1158,11 @@ int run_batch(upow_ctx* ctx, const std::vector<Prepared>& prep, uint64_t max_non
     const uint32_t h_total = (uint32_t)((max_nonce + 0xffff) >> 16);
     uint32_t base = 1;
     while ((double)base * 4 * 65536.0 < e_min && base < 1024) base <<= 1;
+    // item length inside a round: short items keep the warps of one template close together, so little is
+    // hashed beyond a template's answer; long items amortise the per-item set-up (measured: profiles/r02_batch_items.json)
+    uint32_t hc_max = 16;
+    if (const char* e = getenv("UPOW_BATCH_HC")) hc_max = (uint32_t)std::max(1, atoi(e));
+    if (const char* e = getenv("UPOW_BATCH_ROUND")) base = (uint32_t)std::max(1, atoi(e));
     std::vector<Round>& rounds = *rounds_out;
     rounds.clear();
     constexpr int CHUNK = 8;
@@ -1173,7 +1182,7 @@ int run_batch(upow_ctx* ctx, const std::vector<Prepared>& prep, uint64_t max_non
                 uint64_t hr = (uint64_t)base << std::min<uint32_t>(ri / 8, 12);
                 hr = std::min<uint64_t>(std::min<uint64_t>(hr, 4096), h_total - h_done);
                 r.h_lo = h_done; r.h_count = (uint32_t)hr;
-                r.hc = (uint32_t)std::min<uint64_t>(64, hr);   // one item per (template, lgroup) and round, up to 64 H
+                r.hc = (uint32_t)std::min<uint64_t>(hc_max, hr);
                 rounds.push_back(r);
                 for (auto& dp : ctx->devs) {
                     Device& d = *dp;
@@ -1189,6 +1198,7 @@ int run_batch(upow_ctx* ctx, const std::vector<Prepared>& prep, uint64_t max_non
                         a.n_peers++;
                     }
                     a.nonce_hi = max_nonce;
+                    a.n_jobs = n;
                     a.parity = parity; a.round = ri; a.stop_at_first = stop_at_first ? 1 : 0;
                     a.h_lo = r.h_lo; a.h_count = r.h_count; a.hc = r.hc;
                     a.lg_first = (uint32_t)d.index; a.lg_step = (uint32_t)n_dev;
@@ -1209,7 +1219,7 @@ int run_batch(upow_ctx* ctx, const std::vector<Prepared>& prep, uint64_t max_non
                     }
                     CU_TRY(ctx, cudaMemsetAsync(&d.d_ctl->n_active[parity ^ 1], 0, sizeof(unsigned int), st));
                     batch_compact_kernel<<<(n + 255) / 256, 256, 0, st>>>(d.d_active[parity], d.d_active[parity ^ 1], d.d_limit,
-                                                                      d.d_ctl, parity, r.h_lo + r.h_count);
+                                                                      d.d_ctl, parity, r.h_lo + r.h_count, n);
                     CU_TRY(ctx, cudaGetLastError());
                 }
                 parity ^= 1;
@@ -1671,7 +1681,7 @@ extern "C" int upow_sha256_batch(upow_ctx* ctx, uint32_t n, const uint8_t* data,
                 const uint32_t m = k.m_hi - k.m_lo;
                 sha256_batch_kernel<<<(m + 127) / 128, 128, 0, st>>>(
                     dev + 32 * (size_t)m + 8 * (size_t)(m + 1), reinterpret_cast<const unsigned long long*>(dev + 32 * (size_t)m), m,
-                    reinterpret_cast<uint32_t*>(dev));
+                    reinterpret_cast<uint32_t*>(dev), (unsigned long long)(offsets[k.m_hi] - offsets[k.m_lo]) + 16);
             };
             pl.out_bytes = [=](uint32_t c, size_t* off) {
                 *off = 0;
@@ -1716,7 +1726,7 @@ extern "C" int upow_sha256_batch_dev(upow_ctx* ctx, int device_index, uint32_t n
     CU_TRY(ctx, cudaSetDevice(d.id));
     CU_TRY(ctx, cudaEventRecord(d.ev_aux[0], d.stream[0]));
     sha256_batch_kernel<<<(n + 127) / 128, 128, 0, d.stream[0]>>>(d_data, reinterpret_cast<const unsigned long long*>(d_offsets), n,
-                                                                 reinterpret_cast<uint32_t*>(d_out));
+                                                                 reinterpret_cast<uint32_t*>(d_out), ~0ull);
     CU_TRY(ctx, cudaGetLastError());
     CU_TRY(ctx, cudaEventRecord(d.ev_aux[1], d.stream[0]));
     CU_TRY(ctx, cudaStreamSynchronize(d.stream[0]));
