@@ -99,8 +99,6 @@ def test_config5_4096_templates():
     rule = O.Rule(d, O.T0_PREV_HASH)
     prefixes = [O.batch_template(i, d) for i in range(4096)]
     assert len(set(prefixes)) == 4096
-    if not os.path.exists(os.path.join(GOLDEN, "cfg5_min_nonces.u32")):
-        pytest.skip("fixture not generated yet: python -m oracle.gen_golden --cfg5")
     raw = open(os.path.join(GOLDEN, "cfg5_min_nonces.u32"), "rb").read()
     want = list(struct.unpack("<4096I", raw))
     meta = json.load(open(os.path.join(GOLDEN, "cfg5_min_nonces.json")))

@@ -294,6 +294,31 @@ def test_batch_on_two_queues_matches_one(gpu_ctx):
     assert (rc, idx, nonce, digest) == (rc1, idx1, nonce1, digest1) and rc == 0
 
 
+def test_without_peer_access_results_stay_exact(monkeypatch, sweep_fixture):
+    """No peer access between the device slots (forced here with UPOW_NO_P2P=all): finds are not published GPU to
+    GPU, the batch engine relays them through the host once per chunk of rounds, single searches simply run each
+    slot's launch to its own end.  Slower, but every answer is still the exact minimum."""
+    import upow_b200
+    monkeypatch.setenv("UPOW_NO_P2P", "all")
+    with upow_b200.Context(device_ids=[0, 0]) as ctx2:
+        assert ctx2.device_info(0).peer_devices == 0
+        prefix = bytes.fromhex(sweep_fixture["prefix"])
+        _set(ctx2, 0, prefix, make_rule(5.0, O.T0_PREV_HASH))
+        rc, res = ctx2.search_min(0)
+        assert (rc, res.nonce) == (0, 164867)
+        d = 4.0
+        rule = make_rule(d, O.T0_PREV_HASH)
+        templates = [(O.batch_template(i, d), bytes.fromhex(O.T0_PREV_HASH), 4, 16) for i in range(200)]
+        items, _ = ctx2.search_batch(templates)
+        for i in range(0, 200, 7):
+            assert items[i][0] and items[i][1] == c_oracle.min_valid_nonce(templates[i][0], rule)[0]
+        rc, idx, nonce, digest, _ = ctx2.search_any(templates)
+    monkeypatch.delenv("UPOW_NO_P2P")
+    with upow_b200.Context(1) as ctx1:
+        assert ctx1.search_batch(templates)[0] == items
+        assert ctx1.search_any(templates)[:4] == (rc, idx, nonce, digest)
+
+
 @pytest.mark.parametrize("mix", ["v2", "mixed"])
 def test_batch_4096_templates_v2_and_mixed(gpu_ctx, mix):
     """4096 templates of the 108-byte layout (and a mix of both layouts) at an oracle-checkable difficulty: the

@@ -199,6 +199,41 @@ struct GenericTail<Tn, 64, SCHED_FROM> {
     }
 };
 
+// A whole compression on a fully variable block, all eight state words kept (block verifier, batched
+// hashing): the same pipe assignment as the search loops, nothing folded.
+template <class Tn, int T>
+struct FullRounds {
+    static UPOW_HD void run(uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d, uint32_t& e, uint32_t& f, uint32_t& g,
+                            uint32_t& h, uint32_t (&w)[64], const Opaque& q) {
+        constexpr bool F = Tn::ADD != 0;
+        if (T >= 16) {
+            w[T] = add2<F>(add2<F>(add2<F>(w[T - 16], w[T - 7], q), sig0<Tn, T>(w[T - 15], q), q),
+                           sig1<Tn, T>(w[T - 2], q), q);
+        }
+        const uint32_t hk = add2<F>(h, addk<F, Kc(T)>(w[T], q), q);
+        round_core<Tn, T>(a, b, c, d, e, f, g, h, hk, q);
+        FullRounds<Tn, T + 1>::run(a, b, c, d, e, f, g, h, w, q);
+    }
+};
+template <class Tn>
+struct FullRounds<Tn, 64> {
+    static UPOW_HD void run(uint32_t&, uint32_t&, uint32_t&, uint32_t&, uint32_t&, uint32_t&, uint32_t&, uint32_t&,
+                            uint32_t (&)[64], const Opaque&) {}
+};
+template <class Tn>
+UPOW_HD void compress_tuned(uint32_t st[8], const uint32_t (&w16)[16], const Opaque& q) {
+    constexpr bool F = Tn::ADD != 0;
+    uint32_t w[64];
+#if UPOW_DEVICE_CODE
+#pragma unroll
+#endif
+    for (int i = 0; i < 16; i++) w[i] = w16[i];
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+    FullRounds<Tn, 0>::run(a, b, c, d, e, f, g, h, w, q);
+    st[0] = add2<F>(st[0], a, q); st[1] = add2<F>(st[1], b, q); st[2] = add2<F>(st[2], c, q); st[3] = add2<F>(st[3], d, q);
+    st[4] = add2<F>(st[4], e, q); st[5] = add2<F>(st[5], f, q); st[6] = add2<F>(st[6], g, q); st[7] = add2<F>(st[7], h, q);
+}
+
 // =========================================================================================
 // v1: 138-byte message.  Tail words: W0 = bswap(ts) (per launch), W1 = difficulty|b0 b1 (per
 // lane), W2 = b2 b3|0x8000 (per nonce), W3..W14 = 0, W15 = 1104.

@@ -41,8 +41,11 @@ static_assert(sizeof(VerifyRecord) == 192, "VerifyRecord must be 192 bytes");
 
 constexpr int VERIFY_THREADS = 128;
 
+using BulkTune = Tune<1, 0, 0, 0, 0, 0, 0>;   // additions on the fma pipe, as in the search kernels
+// TUNED: the compression with explicit pipe assignment (hot_loop.h compress_tuned); otherwise plain CUDA.
+template <bool TUNED>
 __global__ void __launch_bounds__(VERIFY_THREADS) verify_kernel(const VerifyRecord* recs, uint32_t n, uint8_t* out_valid,
-                                                               uint32_t* out_digests) {
+                                                               uint32_t* out_digests, const __grid_constant__ Opaque q) {
     __shared__ uint4 stage[VERIFY_THREADS * 12];   // 128 records x 192 B
     const uint32_t base = blockIdx.x * VERIFY_THREADS;
     const uint32_t n_here = min((uint32_t)VERIFY_THREADS, n - base);
@@ -73,7 +76,8 @@ __global__ void __launch_bounds__(VERIFY_THREADS) verify_kernel(const VerifyReco
                 if (b == n_blocks - 1 && i == 15) v = len * 8;
                 w[i] = v;
             }
-            compress_unrolled(st, w);
+            if (TUNED) compress_tuned<BulkTune>(st, w, q);
+            else compress_unrolled(st, w);
         }
         uint32_t prev[8];
 #pragma unroll
@@ -98,8 +102,10 @@ __global__ void __launch_bounds__(VERIFY_THREADS) verify_kernel(const VerifyReco
 // with aligned 32-bit loads re-aligned and byte-swapped by one PRMT per word.  The buffer must be
 // readable 8 bytes past its end (the library pads its device copy).  Bound by the alu pipe like the
 // search kernels (about 1300 instructions per 64 bytes), not by HBM.
+template <bool TUNED>
 __global__ void __launch_bounds__(128) sha256_batch_kernel(const uint8_t* data, const unsigned long long* offsets,
-                                                          uint32_t n, uint32_t* out, unsigned long long readable_bytes) {
+                                                          uint32_t n, uint32_t* out, unsigned long long readable_bytes,
+                                                          const __grid_constant__ Opaque q) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const unsigned long long beg = offsets[i];
@@ -137,7 +143,8 @@ __global__ void __launch_bounds__(128) sha256_batch_kernel(const uint8_t* data, 
             w[14] = (uint32_t)((len * 8) >> 32);
             w[15] = (uint32_t)(len * 8);
         }
-        compress_unrolled(st, w);
+        if (TUNED) compress_tuned<BulkTune>(st, w, q);
+        else compress_unrolled(st, w);
     }
 #pragma unroll
     for (int k = 0; k < 8; k++) out[(size_t)i * 8 + k] = bswap32(st[k]);   // digest bytes in order

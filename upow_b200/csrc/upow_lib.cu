@@ -345,8 +345,11 @@ void init_peer_access(upow_ctx* ctx) {
         for (int b = 0; b < n; b++) {
             if (a == b) continue;
             Device& db = *ctx->devs[b];
-            bool ok = da.id == db.id;
-            if (!ok && getenv("UPOW_NO_P2P") == nullptr) {
+            // UPOW_NO_P2P=1: never enable peer access between different GPUs; UPOW_NO_P2P=all: also treat two
+            // slots on the SAME GPU as unreachable (lets a one-GPU box test the host relay of finds)
+            const char* no_p2p = getenv("UPOW_NO_P2P");
+            bool ok = da.id == db.id && !(no_p2p && strcmp(no_p2p, "all") == 0);
+            if (!ok && da.id != db.id && no_p2p == nullptr) {
                 int can = 0;
                 if (cudaDeviceCanAccessPeer(&can, da.id, db.id) == cudaSuccess && can && cudaSetDevice(da.id) == cudaSuccess) {
                     cudaError_t e = cudaDeviceEnablePeerAccess(db.id, 0);
@@ -1521,6 +1524,26 @@ int run_plans(upow_ctx* ctx, const std::vector<ChunkPlan>& plans, std::vector<do
     return UPOW_OK;
 }
 
+// UPOW_BULK_PLAIN=1 selects the plain-CUDA compression in the two bulk kernels (for comparison runs)
+bool bulk_tuned() {
+    static const bool tuned = getenv("UPOW_BULK_PLAIN") == nullptr;
+    return tuned;
+}
+void launch_verify(const VerifyRecord* recs, uint32_t n, uint8_t* valid, uint32_t* digests, cudaStream_t st) {
+    Opaque q;
+    fill_opaque(&q);
+    const uint32_t grid = (n + VERIFY_THREADS - 1) / VERIFY_THREADS;
+    if (bulk_tuned()) verify_kernel<true><<<grid, VERIFY_THREADS, 0, st>>>(recs, n, valid, digests, q);
+    else verify_kernel<false><<<grid, VERIFY_THREADS, 0, st>>>(recs, n, valid, digests, q);
+}
+void launch_sha_batch(const uint8_t* data, const unsigned long long* offsets, uint32_t n, uint32_t* out,
+                      unsigned long long readable, cudaStream_t st) {
+    Opaque q;
+    fill_opaque(&q);
+    if (bulk_tuned()) sha256_batch_kernel<true><<<(n + 127) / 128, 128, 0, st>>>(data, offsets, n, out, readable, q);
+    else sha256_batch_kernel<false><<<(n + 127) / 128, 128, 0, st>>>(data, offsets, n, out, readable, q);
+}
+
 constexpr uint32_t VERIFY_CHUNK = 32768;   // blocks per chunk: 6 MiB of records + 32 KiB verdicts + 1 MiB digests
 static_assert((size_t)VERIFY_CHUNK * (sizeof(VerifyRecord) + 1 + 32) <= LANE_BYTES, "verify chunk does not fit a lane buffer");
 }  // namespace
@@ -1555,9 +1578,8 @@ extern "C" int upow_verify_blocks(upow_ctx* ctx, uint32_t n_blocks, const upow_b
             pl.run = [=](uint32_t c, uint8_t* dev, cudaStream_t st) {
                 uint32_t first;
                 const uint32_t m = span(c, &first);
-                verify_kernel<<<(m + VERIFY_THREADS - 1) / VERIFY_THREADS, VERIFY_THREADS, 0, st>>>(
-                    reinterpret_cast<const VerifyRecord*>(dev), m, dev + off_valid,
-                    out_digests ? reinterpret_cast<uint32_t*>(dev + off_dig) : nullptr);
+                launch_verify(reinterpret_cast<const VerifyRecord*>(dev), m, dev + off_valid,
+                              out_digests ? reinterpret_cast<uint32_t*>(dev + off_dig) : nullptr, st);
             };
             pl.out_bytes = [=](uint32_t c, size_t* off) {
                 uint32_t first;
@@ -1605,8 +1627,8 @@ extern "C" int upow_verify_blocks_dev(upow_ctx* ctx, int device_index, uint32_t 
     Device& d = *ctx->devs[device_index];
     CU_TRY(ctx, cudaSetDevice(d.id));
     CU_TRY(ctx, cudaEventRecord(d.ev_aux[0], d.stream[0]));
-    verify_kernel<<<(n_blocks + VERIFY_THREADS - 1) / VERIFY_THREADS, VERIFY_THREADS, 0, d.stream[0]>>>(
-        reinterpret_cast<const VerifyRecord*>(d_blocks), n_blocks, d_valid, reinterpret_cast<uint32_t*>(d_digests));
+    launch_verify(reinterpret_cast<const VerifyRecord*>(d_blocks), n_blocks, d_valid, reinterpret_cast<uint32_t*>(d_digests),
+                  d.stream[0]);
     CU_TRY(ctx, cudaGetLastError());
     CU_TRY(ctx, cudaEventRecord(d.ev_aux[1], d.stream[0]));
     CU_TRY(ctx, cudaStreamSynchronize(d.stream[0]));
@@ -1679,9 +1701,8 @@ extern "C" int upow_sha256_batch(upow_ctx* ctx, uint32_t n, const uint8_t* data,
             pl.run = [=](uint32_t c, uint8_t* dev, cudaStream_t st) {
                 const Chunk k = ch[c0 + c];
                 const uint32_t m = k.m_hi - k.m_lo;
-                sha256_batch_kernel<<<(m + 127) / 128, 128, 0, st>>>(
-                    dev + 32 * (size_t)m + 8 * (size_t)(m + 1), reinterpret_cast<const unsigned long long*>(dev + 32 * (size_t)m), m,
-                    reinterpret_cast<uint32_t*>(dev), (unsigned long long)(offsets[k.m_hi] - offsets[k.m_lo]) + 16);
+                launch_sha_batch(dev + 32 * (size_t)m + 8 * (size_t)(m + 1), reinterpret_cast<const unsigned long long*>(dev + 32 * (size_t)m),
+                                 m, reinterpret_cast<uint32_t*>(dev), (unsigned long long)(offsets[k.m_hi] - offsets[k.m_lo]) + 16, st);
             };
             pl.out_bytes = [=](uint32_t c, size_t* off) {
                 *off = 0;
@@ -1725,8 +1746,8 @@ extern "C" int upow_sha256_batch_dev(upow_ctx* ctx, int device_index, uint32_t n
     Device& d = *ctx->devs[device_index];
     CU_TRY(ctx, cudaSetDevice(d.id));
     CU_TRY(ctx, cudaEventRecord(d.ev_aux[0], d.stream[0]));
-    sha256_batch_kernel<<<(n + 127) / 128, 128, 0, d.stream[0]>>>(d_data, reinterpret_cast<const unsigned long long*>(d_offsets), n,
-                                                                 reinterpret_cast<uint32_t*>(d_out), ~0ull);
+    launch_sha_batch(d_data, reinterpret_cast<const unsigned long long*>(d_offsets), n, reinterpret_cast<uint32_t*>(d_out), ~0ull,
+                     d.stream[0]);
     CU_TRY(ctx, cudaGetLastError());
     CU_TRY(ctx, cudaEventRecord(d.ev_aux[1], d.stream[0]));
     CU_TRY(ctx, cudaStreamSynchronize(d.stream[0]));
