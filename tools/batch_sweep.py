@@ -22,13 +22,12 @@ with upow_b200.Context(1) as ctx:
 print(json.dumps(best))
 """ % ROOT
 out = []
-for hc in (4, 8, 16, 32, 64):
-    for rnd in (0, 16):
-        env = dict(os.environ, UPOW_BATCH_HC=str(hc))
-        if rnd:
-            env["UPOW_BATCH_ROUND"] = str(rnd)
+for hc in (16, 32, 64):
+    for poll in (1, 2, 4, 8):
+        rnd = 0
+        env = dict(os.environ, UPOW_BATCH_HC=str(hc), UPOW_BATCH_POLL=str(poll))
         r = json.loads(subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True, check=True).stdout.strip().splitlines()[-1])
-        out.append({"hc": hc, "round_base": rnd or "default(64)", "wall_s": r["wall_s"], "ghs": r["ghs"], "overshoot": r["overshoot"]})
+        out.append({"hc": hc, "poll": poll, "wall_s": r["wall_s"], "ghs": r["ghs"], "overshoot": r["overshoot"]})
         print(out[-1], flush=True)
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
 json.dump(out, open(os.path.join(ROOT, "gpurun_out", "batch_items.json"), "w"), indent=1)

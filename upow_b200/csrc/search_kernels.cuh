@@ -546,6 +546,7 @@ struct BatchArgs {
     uint32_t stop_at_first;          // 1: rounds after the first one with a find do nothing (upow_search_any)
     uint32_t h_lo, h_count, hc;      // this round covers H in [h_lo, h_lo + h_count)
     uint32_t lg_first, lg_step, lg_count;
+    uint32_t poll_mask;              // limit[] is re-read when (H & poll_mask) == 0 (a power of two minus one)
     KillSwitch kill;
     Opaque q;                        // see hot_loop.h
 };
@@ -602,7 +603,7 @@ __global__ void __launch_bounds__(256, 3) batch_kernel(const __grid_constant__ B
             // the constant bank, otherwise identical to search_kernel_tuned
             const V1Lane s = v1_lane_setup(job.tail, L);
             for (; H < h_end; H++) {
-                if ((H & (LIMIT_POLL - 1)) == 0) {
+                if ((H & A.poll_mask) == 0) {
                     if (((unsigned long long)H << 16) >= lim) break;
                     lim = ld_volatile_u64(lim_p);
                 }
@@ -616,7 +617,7 @@ __global__ void __launch_bounds__(256, 3) batch_kernel(const __grid_constant__ B
             const V2Consts u = job.v2;   // per-template schedule constants, in registers for the H loop
             const uint32_t lsw = v2_w10_from_L(L);
             for (; H < h_end; H++) {
-                if ((H & (LIMIT_POLL - 1)) == 0) {
+                if ((H & A.poll_mask) == 0) {
                     if (((unsigned long long)H << 16) >= lim) break;
                     lim = ld_volatile_u64(lim_p);
                 }

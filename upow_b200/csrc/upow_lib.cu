@@ -1166,6 +1166,11 @@ int run_batch(upow_ctx* ctx, const std::vector<Prepared>& prep, uint64_t max_non
     uint32_t hc_max = 16;
     if (const char* e = getenv("UPOW_BATCH_HC")) hc_max = (uint32_t)std::max(1, atoi(e));
     if (const char* e = getenv("UPOW_BATCH_ROUND")) base = (uint32_t)std::max(1, atoi(e));
+    // how often a warp re-reads its template's limit inside an item (H values): every hash evaluated after a
+    // template's answer is wasted, and with thousands of templates those tails add up
+    uint32_t poll = 8;
+    if (const char* e = getenv("UPOW_BATCH_POLL")) poll = (uint32_t)std::max(1, atoi(e));
+    while (poll & (poll - 1)) poll &= poll - 1;   // power of two
     std::vector<Round>& rounds = *rounds_out;
     rounds.clear();
     constexpr int CHUNK = 8;
@@ -1206,6 +1211,7 @@ int run_batch(upow_ctx* ctx, const std::vector<Prepared>& prep, uint64_t max_non
                     a.h_lo = r.h_lo; a.h_count = r.h_count; a.hc = r.hc;
                     a.lg_first = (uint32_t)d.index; a.lg_step = (uint32_t)n_dev;
                     a.lg_count = (LGROUPS - a.lg_first + a.lg_step - 1) / a.lg_step;
+                    a.poll_mask = poll - 1;
                     a.kill.word = d.d_kill;
                     fill_opaque(&a.q);
                     if (has_v1) {
