@@ -203,14 +203,19 @@ int upow_set_variant(upow_ctx* ctx, int variant);
 /* No counterpart in the reference.  The sweep of upow_sweep for callers that must not allocate:
  * a host whose own arena already owns all GPU memory, a caller that cannot take the device-wide
  * stall of cudaMalloc/cudaFree, code where creating streams, events or buffers is off limits.
- * Needs no upow_ctx.  The device scratch (work queue, hit counter, hit buffer) is a fixed static
- * array of UPOW_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit, so:
+ * Needs no upow_ctx.  The device scratch (work queue, hit counter, stop word, hit buffer) is a fixed
+ * static array of UPOW_NOALLOC_SCRATCH_BYTES inside the library's device code image; a GPU holds it
+ * from the moment the CUDA runtime loads that image there (with lazy loading: this entry point's first
+ * call on the device) until the process exits, so:
  *   - cap may not exceed UPOW_NOALLOC_MAX_HITS (UPOW_E_ARG otherwise);
- *   - all calls on a device share the array: the library serialises its own calls per device and
- *     runs them synchronously on the legacy default stream, and clears the control block at the
- *     start of each call; GPU work from elsewhere that overlaps a call on the same array races;
- *   - the first call on each device resolves the array's device address and uploads constants:
- *     issue it before any stream capture starts.
+ *   - all calls on a device share the array: the library serialises its own calls per device, runs
+ *     each on the calling thread's per-thread default stream (no stream is created, the host's other
+ *     streams are not synchronised) and waits for it, and clears the control block at the start of each
+ *     call; GPU work from elsewhere that overlaps a call on the same array races;
+ *   - every call looks the array's device address up again (never stale after a device reset); the
+ *     FIRST call on a device also makes the runtime load the kernel and materialise the array, which
+ *     takes device memory once: issue it before the host claims all free memory and before any stream
+ *     capture starts.
  * Calls no cudaMalloc/cudaFree, creates no stream or event.  Output: valid nonces of
  * [nonce_lo, nonce_hi), sorted ascending; *out_count is the true count; UPOW_E_OVERFLOW if it exceeds
  * cap.  Error text: upow_noalloc_last_error(). */

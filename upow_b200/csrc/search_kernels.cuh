@@ -390,41 +390,48 @@ __global__ void __launch_bounds__(BLOCK, MINB) search_kernel_tuned(const __grid_
 
         if (LAYOUT == LAYOUT_V1) {
             const V1Lane s = v1_lane_setup(A.tail, L);
-            for (; H < it.h_end; H += NPT) {
-                if (MODE == MODE_MIN && (H & (LIMIT_POLL - 1)) == 0) {
-                    // test the value read LIMIT_POLL iterations ago, then start the next read: its latency hides
-                    // behind the hashes in between instead of stalling the warp
+            // MODE_MIN walks H in blocks of LIMIT_POLL: at every block boundary the limit read one block ago is
+            // tested and the next read is started (its latency hides behind the block's hashes); the inner loop is
+            // the same instruction stream as the enumerating kernel's.
+            while (H < it.h_end) {
+                uint32_t h_stop = it.h_end;
+                if (MODE == MODE_MIN) {
                     if (((unsigned long long)H << 16) >= lim) break;
                     lim = ld_volatile_u64(&res->limit);
+                    h_stop = min(h_stop, (H | (LIMIT_POLL - 1)) + 1);
                 }
-                uint32_t a64[NPT];
+                for (; H < h_stop; H += NPT) {
+                    uint32_t a64[NPT];
 #pragma unroll
-                for (int j = 0; j < NPT; j++) a64[j] = v1_nonce_a64<Tn>(s, v1_w2(H + j), A.q);   // independent chains
+                    for (int j = 0; j < NPT; j++) a64[j] = v1_nonce_a64<Tn>(s, v1_w2(H + j), A.q);   // independent chains
 #pragma unroll
-                for (int j = 0; j < NPT; j++) {
-                    const bool hit = addu<Tn::ADD != 0>(a64[j], A.rule.sub0, A.q) < A.rule.range0 && (NPT == 1 || H + j < it.h_end);
-                    if (__ballot_sync(0xffffffffu, hit)) {
-                        if (hit) report_hit<MODE>(A.tail, A.rule, A.nonce_lo, A.nonce_hi, ((H + j) << 16) | L, A.sink);
+                    for (int j = 0; j < NPT; j++) {
+                        const bool hit = addu<Tn::ADD != 0>(a64[j], A.rule.sub0, A.q) < A.rule.range0 && (NPT == 1 || H + j < it.h_end);
+                        if (__ballot_sync(0xffffffffu, hit)) {
+                            if (hit) report_hit<MODE>(A.tail, A.rule, A.nonce_lo, A.nonce_hi, ((H + j) << 16) | L, A.sink);
+                        }
                     }
                 }
             }
         } else {
             const uint32_t lsw = v2_w10_from_L(L);
-            for (; H < it.h_end; H += NPT) {
-                if (MODE == MODE_MIN && (H & (LIMIT_POLL - 1)) == 0) {
-                    // test the value read LIMIT_POLL iterations ago, then start the next read: its latency hides
-                    // behind the hashes in between instead of stalling the warp
+            while (H < it.h_end) {
+                uint32_t h_stop = it.h_end;
+                if (MODE == MODE_MIN) {
                     if (((unsigned long long)H << 16) >= lim) break;
                     lim = ld_volatile_u64(&res->limit);
+                    h_stop = min(h_stop, (H | (LIMIT_POLL - 1)) + 1);
                 }
-                uint32_t a64[NPT];
+                for (; H < h_stop; H += NPT) {
+                    uint32_t a64[NPT];
 #pragma unroll
-                for (int j = 0; j < NPT; j++) a64[j] = v2_nonce_a64<Tn>(A.v2, lsw | v2_w10_from_H(H + j), A.q);
+                    for (int j = 0; j < NPT; j++) a64[j] = v2_nonce_a64<Tn>(A.v2, lsw | v2_w10_from_H(H + j), A.q);
 #pragma unroll
-                for (int j = 0; j < NPT; j++) {
-                    const bool hit = addu<Tn::ADD != 0>(a64[j], A.rule.sub0, A.q) < A.rule.range0 && (NPT == 1 || H + j < it.h_end);
-                    if (__ballot_sync(0xffffffffu, hit)) {
-                        if (hit) report_hit<MODE>(A.tail, A.rule, A.nonce_lo, A.nonce_hi, ((H + j) << 16) | L, A.sink);
+                    for (int j = 0; j < NPT; j++) {
+                        const bool hit = addu<Tn::ADD != 0>(a64[j], A.rule.sub0, A.q) < A.rule.range0 && (NPT == 1 || H + j < it.h_end);
+                        if (__ballot_sync(0xffffffffu, hit)) {
+                            if (hit) report_hit<MODE>(A.tail, A.rule, A.nonce_lo, A.nonce_hi, ((H + j) << 16) | L, A.sink);
+                        }
                     }
                 }
             }
@@ -546,7 +553,7 @@ struct BatchArgs {
     uint32_t stop_at_first;          // 1: rounds after the first one with a find do nothing (upow_search_any)
     uint32_t h_lo, h_count, hc;      // this round covers H in [h_lo, h_lo + h_count)
     uint32_t lg_first, lg_step, lg_count;
-    uint32_t poll_mask;              // limit[] is re-read when (H & poll_mask) == 0 (a power of two minus one)
+    uint32_t poll_mask;              // limit[] is re-read every poll_mask + 1 H values (a power of two minus one)
     KillSwitch kill;
     Opaque q;                        // see hot_loop.h
 };
@@ -602,29 +609,31 @@ __global__ void __launch_bounds__(256, 3) batch_kernel(const __grid_constant__ B
             // the hand-specialised loop of hot_loop.h; the per-template words come from the job table instead of
             // the constant bank, otherwise identical to search_kernel_tuned
             const V1Lane s = v1_lane_setup(job.tail, L);
-            for (; H < h_end; H++) {
-                if ((H & A.poll_mask) == 0) {
-                    if (((unsigned long long)H << 16) >= lim) break;
-                    lim = ld_volatile_u64(lim_p);
-                }
-                const uint32_t a64 = v1_nonce_a64<BatchTune>(s, v1_w2(H), A.q);
-                const bool hit = add2<true>(a64, sub0, A.q) < range0;
-                if (__ballot_sync(0xffffffffu, hit)) {
-                    if (hit) batch_report_hit(job, j, (H << 16) | L, A);
+            while (H < h_end) {
+                if (((unsigned long long)H << 16) >= lim) break;
+                lim = ld_volatile_u64(lim_p);
+                const uint32_t h_stop = min(h_end, (H | A.poll_mask) + 1);
+                for (; H < h_stop; H++) {
+                    const uint32_t a64 = v1_nonce_a64<BatchTune>(s, v1_w2(H), A.q);
+                    const bool hit = add2<true>(a64, sub0, A.q) < range0;
+                    if (__ballot_sync(0xffffffffu, hit)) {
+                        if (hit) batch_report_hit(job, j, (H << 16) | L, A);
+                    }
                 }
             }
         } else {
             const V2Consts u = job.v2;   // per-template schedule constants, in registers for the H loop
             const uint32_t lsw = v2_w10_from_L(L);
-            for (; H < h_end; H++) {
-                if ((H & A.poll_mask) == 0) {
-                    if (((unsigned long long)H << 16) >= lim) break;
-                    lim = ld_volatile_u64(lim_p);
-                }
-                const uint32_t a64 = v2_nonce_a64<BatchTune>(u, lsw | v2_w10_from_H(H), A.q);
-                const bool hit = add2<true>(a64, sub0, A.q) < range0;
-                if (__ballot_sync(0xffffffffu, hit)) {
-                    if (hit) batch_report_hit(job, j, (H << 16) | L, A);
+            while (H < h_end) {
+                if (((unsigned long long)H << 16) >= lim) break;
+                lim = ld_volatile_u64(lim_p);
+                const uint32_t h_stop = min(h_end, (H | A.poll_mask) + 1);
+                for (; H < h_stop; H++) {
+                    const uint32_t a64 = v2_nonce_a64<BatchTune>(u, lsw | v2_w10_from_H(H), A.q);
+                    const bool hit = add2<true>(a64, sub0, A.q) < range0;
+                    if (__ballot_sync(0xffffffffu, hit)) {
+                        if (hit) batch_report_hit(job, j, (H << 16) | L, A);
+                    }
                 }
             }
         }

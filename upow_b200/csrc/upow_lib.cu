@@ -1168,7 +1168,7 @@ int run_batch(upow_ctx* ctx, const std::vector<Prepared>& prep, uint64_t max_non
     if (const char* e = getenv("UPOW_BATCH_ROUND")) base = (uint32_t)std::max(1, atoi(e));
     // how often a warp re-reads its template's limit inside an item (H values): every hash evaluated after a
     // template's answer is wasted, and with thousands of templates those tails add up
-    uint32_t poll = 8;
+    uint32_t poll = 2;   // measured (profiles/r02_batch_items.json): 16-H items polled every 2 H give the shortest cfg-5 run
     if (const char* e = getenv("UPOW_BATCH_POLL")) poll = (uint32_t)std::max(1, atoi(e));
     while (poll & (poll - 1)) poll &= poll - 1;   // power of two
     std::vector<Round>& rounds = *rounds_out;
