@@ -10,6 +10,10 @@ CSRC = os.path.join(HERE, "csrc")
 # UPOW_CHECKED=1 selects the build with device-side index asserts (tools/sanitizer_target.py)
 CHECKED = os.environ.get("UPOW_CHECKED", "") not in ("", "0")
 LIB = os.path.join(HERE, "libupow_b200_checked.so" if CHECKED else "libupow_b200.so")
+# experiments: UPOW_LIB=<path> builds / loads another library file, UPOW_NVCC_EXTRA="<flags>" is appended to the nvcc line
+if os.environ.get("UPOW_LIB"):
+    LIB = os.path.abspath(os.environ["UPOW_LIB"])
+NVCC_EXTRA = os.environ.get("UPOW_NVCC_EXTRA", "").split()
 SOURCES = ["upow_lib.cu", "microbench.cu", "noalloc.cu"]
 HEADERS = ["kernels.cuh", "search_kernels.cuh", "hot_loop.h", "sha256_core.h", "template_prep.h", os.path.join("..", "..", "include", "upow_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
@@ -35,7 +39,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB
     all_variants = os.environ.get("UPOW_ALL_VARIANTS", "") not in ("", "0")   # the 13 slower builds of round 1 too
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-DUPOW_CHECKED"] if CHECKED else []) + (["-DUPOW_ALL_VARIANTS"] if all_variants else []) + (["-Xptxas", "-v"] if verbose else []) + \
+    cmd = [_nvcc()] + NVCC_FLAGS + (["-DUPOW_CHECKED"] if CHECKED else []) + (["-DUPOW_ALL_VARIANTS"] if all_variants else []) + (["-Xptxas", "-v"] if verbose else []) + NVCC_EXTRA + \
           ["-I", CSRC, "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     subprocess.check_call(cmd)
     return LIB

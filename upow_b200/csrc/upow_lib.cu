@@ -290,6 +290,9 @@ struct Variant {
     { NAME, { { search_kernel_tuned<LAYOUT_V1, MODE_MIN, TN, MINB, BLOCK, NPT>, search_kernel_tuned<LAYOUT_V1, MODE_ENUM, TN, MINB, BLOCK, NPT> }, \
               { search_kernel_tuned<LAYOUT_V2, MODE_MIN, TN, MINB, BLOCK, NPT>, search_kernel_tuned<LAYOUT_V2, MODE_ENUM, TN, MINB, BLOCK, NPT> } }, BLOCK }
 #define TN(...) Tune<__VA_ARGS__>
+#ifndef UPOW_MINB
+#define UPOW_MINB 3   // resident 256-thread blocks per SM the default build is compiled for
+#endif
 const Variant VARIANTS[] = {
     UPOW_PLAIN_VARIANT("plain: nvcc-chosen pipes"),
 #ifdef UPOW_ALL_VARIANTS
@@ -301,7 +304,7 @@ const Variant VARIANTS[] = {
     UPOW_TUNED_VARIANT("add only on fma", TN(1, 0, 0, 0, 0, 0), 3),
     UPOW_TUNED_VARIANT("add+shr, 7-add rounds", TN(1, 1, 0, 0, 0, 0, 0), 3),
 #endif
-    UPOW_TUNED_VARIANT("add only, 7-add rounds", TN(1, 0, 0, 0, 0, 0, 0), 3),
+    UPOW_TUNED_VARIANT("add only, 7-add rounds", TN(1, 0, 0, 0, 0, 0, 0), UPOW_MINB),
 #ifdef UPOW_ALL_VARIANTS
     UPOW_TUNED_VARIANT("add, 7-add, shr via IMAD.HI", TN(1, 2, 0, 0, 0, 0, 0), 3),
     UPOW_TUNED_VARIANT("add, 7-add, shr via IMAD.HI on 2/4 words", TN(1, 2, 0, 0, 0, 0, 0, 2), 3),
