@@ -80,6 +80,31 @@ uint32_t hh_tuned_a64(const Tail* t, uint32_t nonce) {
     return v2_nonce_a64<Tn>(u, v2_w10_from_L(L) | v2_w10_from_H(H), q);
 }
 
+// whole-message SHA-256 through compress_tuned (the compression of the block verifier / batched hashing kernels)
+void hh_sha256_tuned(const uint8_t* msg, uint64_t len, uint8_t out[32]) {
+    using Tn = Tune<1, 0, 0, 0, 0, 0, 0>;
+    Opaque q;
+    fill_opaque(&q);
+    uint32_t st[8];
+    memcpy(st, H_INIT, sizeof st);
+    uint8_t buf[128];
+    uint64_t off = 0;
+    auto block = [&](const uint8_t* p) {
+        uint32_t w[16];
+        for (int i = 0; i < 16; i++) w[i] = load_be32(p + 4 * i);
+        compress_tuned<Tn>(st, w, q);
+    };
+    for (; off + 64 <= len; off += 64) block(msg + off);
+    memset(buf, 0, sizeof buf);
+    const uint64_t rem = len - off;
+    memcpy(buf, msg + off, rem);
+    buf[rem] = 0x80;
+    const uint64_t total = rem + 9 <= 64 ? 64 : 128, bits = len * 8;
+    for (int i = 0; i < 8; i++) buf[total - 1 - i] = (uint8_t)(bits >> (8 * i));
+    for (uint64_t o = 0; o < total; o += 64) block(buf + o);
+    for (int i = 0; i < 8; i++) store_be32(out + 4 * i, st[i]);
+}
+
 int hh_prefilter(const Rule* r, uint32_t a64) { return a64 + r->sub0 < r->range0; }
 int hh_rule_accepts(const Rule* r, const uint32_t d[8]) { return rule_accepts(*r, d); }
 

@@ -151,7 +151,10 @@ __device__ __forceinline__ bool killed(const KillSwitch& k) {
 // How often the H loop of a MODE_MIN search re-reads `limit` (H values, power of two).  The read is software
 // pipelined (issued at one poll, tested at the next), so a find anywhere stops every warp within twice this
 // many hashes per lane instead of at its next item, and no warp ever waits for the load.
-constexpr uint32_t LIMIT_POLL = 8;
+#ifndef UPOW_LIMIT_POLL
+#define UPOW_LIMIT_POLL 8
+#endif
+constexpr uint32_t LIMIT_POLL = UPOW_LIMIT_POLL;
 
 // Rounds FIRST..63 of the tail compression, fully unrolled, schedule expanded in place.
 // `s` is the state BEFORE round FIRST; returns a after round 63 (digest word 0 minus mid[0]).
