@@ -211,13 +211,42 @@ def cfg5_fixture(log, workers):
     log(f"cfg5 fixture: fingerprint {fp}, {total} hashes, {time.time() - t0:.0f} s")
 
 
+def blockfmt_vectors():
+    """block_to_bytes / split_block_content (upow/manager.py:384-419) run verbatim on random blocks.  The reference's
+    split_block_content sends the address through fastecdsa (bytes -> curve point -> string), which is not
+    installed here and is the identity for valid points; for this run bytes_to_string is replaced by the plain
+    formatting of the bytes (hex / base58), everything else is the reference's own code."""
+    mgr = ref_loader.load_manager()
+    mgr.bytes_to_string = lambda b: b.hex() if len(b) == 64 else O.b58encode(b)
+    rng = random.Random(20261107)
+    out = []
+    for i in range(24):
+        v2 = i % 3 == 1
+        address = O.b58encode(bytes([42 + (i & 1)]) + rng.randbytes(32)) if v2 else rng.randbytes(64).hex()
+        d = rng.choice(["6.0", "6.3", "7.9", "10.5", "0.1", "25.5", 6, 6.5])
+        block = {"address": address, "merkle_tree": rng.randbytes(32).hex(), "timestamp": rng.randrange(1, 1 << 32),
+                 "difficulty": d, "random": rng.randrange(0, 1 << 32)}
+        prev = rng.randbytes(32).hex()
+        content = mgr.block_to_bytes(prev, block)
+        split = mgr.split_block_content(content.hex())
+        out.append({"last_block_hash": prev, "block": block, "content": content.hex(),
+                    "split": [split[0], split[1], split[2], split[3], str(split[4]), split[5]]})
+    with open(os.path.join(GOLDEN, "blockfmt_vectors.json"), "w") as f:
+        json.dump(out, f, indent=1)
+    print(f"{len(out)} block wire-format vectors")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--sweep", action="store_true")
+    ap.add_argument("--blockfmt", action="store_true", help="only: block_to_bytes / split_block_content vectors")
     ap.add_argument("--cfg4", action="store_true")
     ap.add_argument("--cfg5", action="store_true")
     ap.add_argument("--workers", type=int, default=os.cpu_count() or 1)
     args = ap.parse_args()
+    if args.blockfmt:
+        blockfmt_vectors()
+        return
     if args.cfg4 or args.cfg5:
         os.makedirs(GOLDEN, exist_ok=True)
         logf = open(os.path.join(GOLDEN, "cfg_pins.log"), "a")
