@@ -59,3 +59,57 @@ def test_windowed_search_and_sweep_match_the_c_oracle(gpu_ctx, prefix, prev, d, 
         assert bytes(res.digest) == hashlib.sha256(prefix + want.to_bytes(4, "little")).digest()
     got, _ = gpu_ctx.sweep(3, lo, hi)
     assert got == c_oracle.all_valid_nonces(prefix, rule, lo, hi)[0]
+
+
+@pytest.mark.gpu
+@settings(max_examples=25, **COMMON)
+@given(prefix=PREFIX, prev=st.binary(min_size=32, max_size=32), d=st.sampled_from([2.0, 2.5, 3.0, 3.4]),
+       cap=st.integers(64, 3000), backwards=st.booleans(), tile=st.sampled_from([0, 1 << 16]))
+def test_rollover_search_matches_the_oracle_in_both_directions(gpu_ctx, prefix, prev, d, cap, backwards, tile):
+    """Timestamp rollover over a nonce space cut to `cap`: the first valid (rollover index, nonce) in search order,
+    forwards (benchmark order) and backwards (what a live miner uses), against the hashlib loop per timestamp."""
+    rule = O.Rule(d, prev.hex())
+    ts0 = O.get_timestamp(prefix)
+    max_roll = 40
+    want = None
+    for k in range(max_roll + 1):
+        ts = (ts0 - k if backwards else ts0 + k) & 0xFFFFFFFF
+        n = O.min_valid_nonce(O.set_timestamp(prefix, ts), rule, 0, 1, cap)
+        if n is not None:
+            want = (k, ts, n)
+            break
+    gpu_ctx.set_template(4, prefix, prev, rule.int_difficulty, rule.charset_count)
+    rc, res = gpu_ctx.search_min(4, max_nonce=cap, max_rollovers=max_roll, rollover_backwards=backwards, tile_nonces=tile)
+    if want is None:
+        assert rc == 1 and res.found == 0
+    else:
+        assert rc == 0 and (res.rollovers, res.timestamp, res.nonce) == want
+        assert bytes(res.digest) == O.digest_of(O.set_timestamp(prefix, want[1]), want[2])
+
+
+@pytest.mark.gpu
+@settings(max_examples=12, **COMMON)
+@given(seeds=st.lists(st.integers(0, 2 ** 31), min_size=1, max_size=40, unique=True),
+       d=st.sampled_from([1.5, 2.0, 3.0, 3.7]), cap_log2=st.sampled_from([12, 16, 32]))
+def test_batch_engine_matches_the_c_oracle_on_random_templates(gpu_ctx, seeds, d, cap_log2):
+    """Random templates of both layouts in one batch, bounded and unbounded nonce space: every minimum (or
+    'none below the bound') equals the C oracle's; search_any picks the lowest index of the earliest round."""
+    import random
+    temps, wants = [], []
+    for s in seeds:
+        rng = random.Random(s)
+        prefix = rng.randbytes(134 if s % 3 else 104)
+        prev = rng.randbytes(32)
+        rule = O.Rule(d, prev.hex())
+        temps.append((prefix, prev, rule.int_difficulty, rule.charset_count))
+        wants.append(c_oracle.min_valid_nonce(prefix, rule, 0, 1, 1 << cap_log2, threads=1)[0])
+    items, _ = gpu_ctx.search_batch(temps, max_nonce=(1 << cap_log2) & 0xFFFFFFFF if cap_log2 < 32 else 0)
+    for (found, nonce, digest), want, t in zip(items, wants, temps):
+        assert (found, nonce if found else None) == (want is not None, want)
+        if found:
+            assert digest == hashlib.sha256(t[0] + nonce.to_bytes(4, "little")).digest()
+    rc, idx, nonce, digest, _ = gpu_ctx.search_any(temps, max_nonce=(1 << cap_log2) if cap_log2 < 32 else 0)
+    if all(w is None for w in wants):
+        assert rc == 1
+    else:
+        assert rc == 0 and nonce == wants[idx]
