@@ -274,6 +274,33 @@ def test_two_physical_gpus_same_answers(sweep_fixture):
         assert ctx2.device_info(0).peer_devices == 1
 
 
+@pytest.mark.parametrize("n_slots", [3, 5])
+def test_uneven_lgroup_classes_same_answers(gpu_ctx, sweep_fixture, n_slots):
+    """2048 lgroups do not divide evenly over 3 or 5 device slots: the classes differ in size by one, every nonce
+    still belongs to exactly one slot, and every answer equals the single-device / oracle answer."""
+    import upow_b200
+    prefix = bytes.fromhex(sweep_fixture["prefix"])
+    ns = sweep_fixture["nonces"]
+    with upow_b200.Context(device_ids=[0] * n_slots) as ctx:
+        _set(ctx, 0, prefix, make_rule(5.0, O.T0_PREV_HASH))
+        for start_idx in (0, 17, 400):
+            start = ns[start_idx - 1] + 1 if start_idx else 0
+            rc, res = ctx.search_min(0, start)
+            assert (rc, res.nonce) == (0, ns[start_idx])
+            assert all(res.per_device_hashes[i] > 0 for i in range(n_slots))
+        got, _ = ctx.sweep(0, 0, 1 << 27)
+        assert got == [n for n in ns if n < (1 << 27)]
+        p3, r3 = O.t0_prefix(3.0, 2), make_rule(3.0, O.T0_PREV_HASH)
+        cap = max(O.min_valid_nonce(p3, r3) // 3, 256)
+        want = O.first_valid_with_rollover(p3, r3, 200, cap)
+        _set(ctx, 1, p3, r3)
+        rc, res = ctx.search_min(1, max_nonce=cap, max_rollovers=200)
+        assert rc == 0 and (res.timestamp, res.nonce) == want
+        d = 4.0
+        templates = [(O.batch_template(i, d), bytes.fromhex(O.T0_PREV_HASH), 4, 16) for i in range(40)]
+        assert ctx.search_batch(templates)[0] == gpu_ctx.search_batch(templates)[0]
+
+
 def test_batch_on_two_queues_matches_one(gpu_ctx):
     """The batch engine with two device slots on GPU 0: each takes half of every template's lgroups and the
     finds reach the other slot's limit array; answers equal the single-queue run and the oracle."""
