@@ -38,7 +38,10 @@ def main():
     rng = random.Random(12)
     stats = {"ok": 0, "cancelled": 0, "deadline": 0, "batch": 0, "sweep": 0}
     t_end = time.time() + seconds
-    for ids in ([0], [0, 0, 0]):
+    configs = [[0], [0, 0, 0]]
+    if os.environ.get("UPOW_STRESS_DEVICES"):      # e.g. "0,1": physical GPUs, finds through NVLink peer memory
+        configs = [[int(x) for x in os.environ["UPOW_STRESS_DEVICES"].split(",")]] * 2
+    for ids in configs:
         with upow_b200.Context(device_ids=ids) as ctx:
             t_ctx_end = time.time() + seconds / 2
             while time.time() < t_ctx_end:
