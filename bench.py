@@ -487,9 +487,16 @@ def main():
     n_gpus = world if world > 1 else max(args.gpus, 1)
     multi = None
     if n_gpus > 1:
+        p16, r16 = t0_prefix_and_rule(16.0, T0_TIMESTAMP)
+        # the same fixed-work search on ONE GPU (4 timestamps), for a like-for-like single-GPU figure: the search
+        # kernel (MODE_MIN, with its limit polls) is 0.5 % slower than the enumerating sweep kernel timed at N = 1
+        ctx.set_template(49, p16, r16.prev_hash, r16.n_int, r16.charset_count)
+        ctx.search_min(49, max_rollovers=1)
+        t0 = time.perf_counter()
+        rc, res1 = ctx.search_min(49, max_rollovers=3)
+        fixed_1gpu = res1.hashes_done / (time.perf_counter() - t0) / 1e9
         ctx.close()
         ctx = upow_b200.Context(device_ids=list(range(n_gpus)))
-        p16, r16 = t0_prefix_and_rule(16.0, T0_TIMESTAMP)
         per_step_ts = 4 * n_gpus
         for k in range(4):
             ctx.set_template(50 + k, with_timestamp(p16, T0_TIMESTAMP + 1000 * k), r16.prev_hash, r16.n_int, r16.charset_count)
@@ -525,7 +532,7 @@ def main():
         multi = {"value": m_hashes / m_elapsed / 1e9, "elapsed": m_elapsed, "launches": m_launches,
                  "e2e": me_hashes / me_elapsed / 1e9, "device_ms_per_step": statistics.mean(m_dev_ms),
                  "h2d": (len(p16) + 32 + 8) + 128 * per_step_ts * n_gpus, "d2h": 128 * per_step_ts * n_gpus,
-                 "clocks": sampler.summary(),
+                 "clocks": sampler.summary(), "fixed_1gpu": fixed_1gpu,
                  "peer_devices": [ctx.device_info(i).peer_devices for i in range(n_gpus)]}
 
     # ---- the BASELINE configs through the same context (answers asserted) ----
@@ -578,6 +585,8 @@ def main():
     if multi is not None:
         config["device_ms_per_step"] = multi["device_ms_per_step"]
         config["peer_devices"] = multi["peer_devices"]
+        config["fixed_work_1gpu_ghs"] = multi["fixed_1gpu"]
+        config["scaling_vs_same_search_on_1gpu"] = multi["value"] / (n_gpus * multi["fixed_1gpu"])
     config.update(extra)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
