@@ -121,7 +121,9 @@ typedef struct upow_block {
 
 /* Creates a context driving n_devices GPUs (device_ids == NULL: devices 0..n-1; n_devices == 0:
  * every visible device, at most UPOW_MAX_DEVICES).  Replaces the worker-pool set-up of
- * miner.py:139-148 (one OS process per worker) by one host thread per GPU. */
+ * miner.py:139-148 (one OS process per worker): one calling thread queues launches on every GPU, the GPUs
+ * share each nonce space (GPU g of N takes the nonces whose bits 5..15 are congruent to g mod N) and tell
+ * each other about finds through peer memory where peer access exists. */
 int upow_init(int n_devices, const int* device_ids, upow_ctx** out_ctx);
 int upow_destroy(upow_ctx* ctx);
 int upow_device_count(const upow_ctx* ctx);
@@ -152,14 +154,14 @@ int upow_search_min(upow_ctx* ctx, int slot, uint64_t start_nonce, uint64_t stri
 int upow_sweep(upow_ctx* ctx, int slot, uint64_t nonce_lo, uint64_t nonce_hi, uint32_t* out_nonces, uint64_t cap,
                uint64_t* out_count, upow_result* stats);
 
-/* n_templates independent searches (minimum valid nonce in [0, max_nonce) of each template),
- * templates sharded over the GPUs, per-template midstates held in device memory.  Corresponds to
+/* n_templates independent searches (minimum valid nonce in [0, max_nonce) of each template); every GPU
+ * holds all per-template midstates and searches its share of every template's nonces.  Corresponds to
  * running miner.py:83-98 once per template.  stats may be NULL. */
 int upow_search_batch(upow_ctx* ctx, uint32_t n_templates, const upow_template* templates, uint64_t max_nonce,
                       upow_batch_item* results, upow_result* stats);
 
-/* The first success over many templates: every template advances through the nonce space in equal
- * rounds; the call returns after the earliest round in which any template has a valid nonce, with
+/* The first success over many templates: every template advances through the nonce space in rounds
+ * (nonce ranges that are the same for all templates and do not depend on the number of GPUs); the call returns after the earliest round in which any template has a valid nonce, with
  * the lowest template index among that round's finds (so the answer does not depend on the number
  * of GPUs) and that template's minimum nonce.  This is what a miner wants when one template's 2^32
  * nonces per second are not enough work for a B200: vary timestamp / transaction subset / address
@@ -182,7 +184,9 @@ int upow_verify_blocks_dev(upow_ctx* ctx, int device_index, uint32_t n_blocks, c
 /* SHA-256 of n variable-length messages: message i is data[offsets[i] .. offsets[i+1]) (offsets has
  * n+1 entries, non-decreasing); out receives 32 bytes per message.  This is the per-transaction hashing
  * of upow/node/main.py:692 and upow/manager.py:365-378 (merkle tree) and Transaction.hash
- * (upow/upow_transactions/transaction.py:85-88) in one call.  Messages are split over the GPUs. */
+ * (upow/upow_transactions/transaction.py:85-88) in one call.  Messages are split over the GPUs and staged
+ * through pinned buffers in chunks; a single message must fit one 8 MiB staging buffer (UPOW_E_ARG otherwise;
+ * the _dev variant has no such limit). */
 int upow_sha256_batch(upow_ctx* ctx, uint32_t n, const uint8_t* data, const uint64_t* offsets, uint8_t* out,
                       upow_result* stats);
 /* The same for data that already lives on the context's GPU number device_index: d_data, d_offsets and
