@@ -438,6 +438,33 @@ def test_cancel_before_search_start_is_honoured(gpu_ctx):
     assert (rc, res.nonce) == (0, 62804)
 
 
+def test_cancel_stops_a_running_batch_and_a_running_sweep(gpu_ctx):
+    """upow_cancel from another thread while the batch engine (rounds queued on the device) or a full sweep is
+    running: the call returns CANCELLED long before its work would have ended, and the context stays usable."""
+    import upow_b200
+    r16 = make_rule(16.0, O.T0_PREV_HASH)
+    temps = [(O.t0_prefix(16.0, 1, O.T0_TIMESTAMP + i), bytes.fromhex(O.T0_PREV_HASH), 16, 16) for i in range(256)]
+    timer = threading.Timer(0.15, gpu_ctx.cancel)
+    t0 = time.time()
+    timer.start()
+    with pytest.raises(upow_b200.UpowError) as e:        # 256 x 2^32 hashes would take a minute
+        gpu_ctx.search_batch(temps)
+    timer.join()
+    assert e.value.code == upow_b200.UPOW_CANCELLED and time.time() - t0 < 3
+    _set(gpu_ctx, 0, O.t0_prefix(16.0), r16)
+    timer = threading.Timer(0.05, gpu_ctx.cancel)
+    timer.start()
+    with pytest.raises(upow_b200.UpowError) as e:
+        gpu_ctx.sweep(0, 0, 1 << 32)
+    timer.join()
+    assert e.value.code == upow_b200.UPOW_CANCELLED
+    _set(gpu_ctx, 0, O.t0_prefix(4.0), make_rule(4.0, O.T0_PREV_HASH))
+    rc, res = gpu_ctx.search_min(0)
+    assert (rc, res.nonce) == (0, 62804)
+    items, _ = gpu_ctx.search_batch([(O.batch_template(i, 4.0), bytes.fromhex(O.T0_PREV_HASH), 4, 16) for i in range(8)])
+    assert all(f for f, _, _ in items)
+
+
 def test_backwards_rollover_order(gpu_ctx):
     """rollover_backwards: timestamps ts, ts-1, ts-2, ... (what a live miner needs: the node rejects timestamps
     in the future, upow/manager.py:456-460).  First valid (rollover index, nonce) in that order."""

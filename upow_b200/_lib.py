@@ -205,7 +205,7 @@ class Context:
         count = C.c_uint64(0)
         stats = Result()
         rc = self._L.upow_sweep(self._h, slot, nonce_lo, nonce_hi, buf, cap, C.byref(count), C.byref(stats))
-        if rc < 0:
+        if rc != UPOW_OK:      # errors, and UPOW_CANCELLED: a partial set must not pass for the whole one
             raise UpowError(rc, "upow_sweep", self._err())
         return list(buf[: count.value]), stats
 
@@ -217,7 +217,7 @@ class Context:
         items = (BatchItem * n)()
         stats = Result()
         rc = self._L.upow_search_batch(self._h, n, arr, max_nonce, items, C.byref(stats))
-        if rc < 0:
+        if rc != UPOW_OK:      # errors, and UPOW_CANCELLED: the results of an interrupted batch mean nothing
             raise UpowError(rc, "upow_search_batch", self._err())
         return [(bool(it.found), it.nonce, bytes(it.digest)) for it in items], stats
 
